@@ -1,0 +1,600 @@
+// context.cu — the `forma_rt` handle (TraceModel, tracer.rs:12-17, plus its device mirror) and the
+// C ABI of include/forma_rt.h.  No CPU fallback: every render entry point launches CUDA kernels.
+#include <cfloat>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/forma_rt.h"
+#include "json.hpp"
+#include "kernels.hpp"
+#include "lbvh.hpp"
+#include "png.hpp"
+#include "scene.hpp"
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+#define CU_TRY(expr)                                                                                   \
+    do {                                                                                               \
+        cudaError_t e__ = (expr);                                                                      \
+        if (e__ != cudaSuccess)                                                                        \
+            return fail(FORMA_RT_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));          \
+    } while (0)
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc((void**)&p, (n ? n : 1) * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    cudaError_t upload(const std::vector<T>& v, cudaStream_t s) {
+        cudaError_t e = ensure(v.size());
+        if (e != cudaSuccess || v.empty()) return e;
+        return cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s);
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+constexpr int kSmemStageLimit = 96 * 1024;   // stage spheres+tris in shared memory up to this size
+constexpr uint32_t kBvhThreshold = 2048;     // ACCEL_AUTO: LBVH at or above this many spheres
+
+}  // namespace
+
+struct forma_rt {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_k0 = nullptr, ev_k1 = nullptr;
+    uint32_t width = 0, height = 0;
+    uint64_t seed = 0;
+    uint32_t flags = 0, accel = FORMA_RT_ACCEL_AUTO;
+    forma::Scene scene;
+    bool scene_dirty = true;
+    uint32_t frame = 0;  // update() call counter -> sample index of the interactive frame
+
+    // packed scene (host copies kept for re-upload after set_object)
+    DevBuf<float4> d_spheres, d_tris, d_planes, d_material;
+    DevBuf<int> d_sphere_obj, d_tri_obj, d_plane_obj, d_kindmat, d_ids;
+    DevBuf<forma::Segment> d_segments;
+    forma::LbvhDevice bvh;
+    forma::SceneView view{};
+
+    // frame buffers
+    DevBuf<uint8_t> d_rgb;
+    DevBuf<float4> d_sum;
+    DevBuf<int32_t> d_prim;
+    DevBuf<float> d_t;
+    unsigned long long* d_rays = nullptr;
+    unsigned long long* h_rays = nullptr;  // pinned
+
+    std::vector<void*> scratch;
+    forma_rt_stats stats{};
+    int sm_count = 0, clock_khz = 0;
+
+    ~forma_rt() {
+        if (device < 0) return;  // host-only handle owns no device resources
+        cudaSetDevice(device);
+        if (stream) cudaStreamSynchronize(stream);
+        for (void* p : scratch) cudaFree(p);
+        d_spheres.release(); d_tris.release(); d_planes.release(); d_material.release();
+        d_sphere_obj.release(); d_tri_obj.release(); d_plane_obj.release(); d_kindmat.release(); d_ids.release();
+        d_segments.release(); d_rgb.release(); d_sum.release(); d_prim.release(); d_t.release();
+        bvh.release();
+        if (d_rays) cudaFree(d_rays);
+        if (h_rays) cudaFreeHost(h_rays);
+        for (cudaEvent_t e : {ev_begin, ev_end, ev_k0, ev_k1}) if (e) cudaEventDestroy(e);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+namespace {
+
+// Scene.objects -> the segment / SoA layout of device_scene.hpp, uploaded on ctx->stream.
+int upload_scene(forma_rt* c) {
+    using namespace forma;
+    const auto& objs = c->scene.objects;
+    std::vector<float4> spheres, tris, planes, material(objs.size());
+    std::vector<int> sphere_obj, tri_obj, plane_obj, kindmat(objs.size()), ids(objs.size());
+    std::vector<Segment> segments;
+
+    size_t i = 0;
+    const size_t n = objs.size();
+    do {  // one segment per run of non-plane objects, closed by the plane that follows it (if any)
+        Segment g;
+        g.sph_begin = (int)spheres.size();
+        g.tri_begin = (int)(tris.size() / 3);
+        size_t j = i;
+        for (; j < n && objs[j].kind != FORMA_RT_PLANE; ++j) {
+            const forma_rt_object& o = objs[j];
+            if (o.kind == FORMA_RT_SPHERE) {
+                spheres.push_back(make_float4(o.a[0], o.a[1], o.a[2], o.b[0]));
+                sphere_obj.push_back((int)j);
+            } else {
+                V3 v0{o.a[0], o.a[1], o.a[2]}, v1{o.b[0], o.b[1], o.b[2]}, v2{o.c[0], o.c[1], o.c[2]};
+                V3 e1 = v1 - v0, e2 = v2 - v0;
+                V3 nrm = unit(cross(e1, e2));
+                tris.push_back(make_float4(v0.x, v0.y, v0.z, nrm.x));
+                tris.push_back(make_float4(e1.x, e1.y, e1.z, nrm.y));
+                tris.push_back(make_float4(e2.x, e2.y, e2.z, nrm.z));
+                tri_obj.push_back((int)j);
+            }
+        }
+        g.sph_end = (int)spheres.size();
+        g.tri_end = (int)(tris.size() / 3);
+        g.plane = -1;
+        if (j < n) {  // objs[j] is a plane
+            const forma_rt_object& o = objs[j];
+            g.plane = (int)plane_obj.size();
+            planes.push_back(make_float4(o.a[0], o.a[1], o.a[2], 0.0f));
+            planes.push_back(make_float4(o.b[0], o.b[1], o.b[2], 0.0f));
+            planes.push_back(make_float4(o.c[0], o.c[1], o.c[2], 0.0f));
+            plane_obj.push_back((int)j);
+            ++j;
+        }
+        if (g.sph_end > g.sph_begin || g.tri_end > g.tri_begin || g.plane >= 0) segments.push_back(g);
+        i = j;
+    } while (i < n);
+
+    uint32_t ns = 0, np = 0, nt = 0;
+    for (size_t k = 0; k < n; ++k) {
+        const forma_rt_object& o = objs[k];
+        material[k] = make_float4(o.color[0], o.color[1], o.color[2], o.fuzz);
+        int kind = o.kind == FORMA_RT_SPHERE ? FORMA_RT_SPHERE : (o.kind == FORMA_RT_PLANE ? FORMA_RT_PLANE : FORMA_RT_TRIANGLE);
+        kindmat[k] = kind | ((o.material & 0xff) << 8);  // material is a u8 in the reference
+        ids[k] = o.id;
+        (kind == FORMA_RT_SPHERE ? ns : kind == FORMA_RT_PLANE ? np : nt)++;
+    }
+
+    cudaStream_t s = c->stream;
+    CU_TRY(c->d_spheres.upload(spheres, s));
+    CU_TRY(c->d_tris.upload(tris, s));
+    CU_TRY(c->d_planes.upload(planes, s));
+    CU_TRY(c->d_material.upload(material, s));
+    CU_TRY(c->d_sphere_obj.upload(sphere_obj, s));
+    CU_TRY(c->d_tri_obj.upload(tri_obj, s));
+    CU_TRY(c->d_plane_obj.upload(plane_obj, s));
+    CU_TRY(c->d_kindmat.upload(kindmat, s));
+    CU_TRY(c->d_ids.upload(ids, s));
+    CU_TRY(c->d_segments.upload(segments, s));
+    CU_TRY(cudaStreamSynchronize(s));  // the host vectors die at return
+
+    SceneView& v = c->view;
+    v.spheres = c->d_spheres.p; v.sphere_obj = c->d_sphere_obj.p;
+    v.tris = c->d_tris.p; v.tri_obj = c->d_tri_obj.p;
+    v.planes = c->d_planes.p; v.plane_obj = c->d_plane_obj.p;
+    v.segments = c->d_segments.p; v.material = c->d_material.p;
+    v.kindmat = c->d_kindmat.p; v.ids = c->d_ids.p;
+    v.n_segments = (int)segments.size();
+    v.n_spheres = (int)ns; v.n_tris = (int)nt; v.n_planes = (int)np;
+    v.bvh_nodes = nullptr;
+
+    // acceleration structure: LBVH over the spheres when asked for / when the scan would be long.
+    // The tree needs every sphere in one segment (planes, if any, first in the list or absent).
+    bool want_bvh = c->accel == FORMA_RT_ACCEL_LBVH || (c->accel == FORMA_RT_ACCEL_AUTO && ns >= kBvhThreshold);
+    bool one_run = true;
+    for (const Segment& g : segments)
+        if (g.sph_end > g.sph_begin && !(g.sph_begin == 0 && g.sph_end == (int)ns)) one_run = false;
+    c->stats.bvh_nodes = 0;
+    c->stats.accel_in_use = FORMA_RT_ACCEL_BRUTE;
+    if (want_bvh && ns >= 2) {
+        if (!one_run)
+            return fail(FORMA_RT_EINVAL, "LBVH needs all spheres in one plane-free run of Scene.objects; use FORMA_RT_ACCEL_BRUTE");
+        cudaError_t e = c->bvh.build(c->d_spheres.p, (int)ns, s);
+        if (e != cudaSuccess) return fail(FORMA_RT_ECUDA, std::string("LBVH build: ") + cudaGetErrorString(e));
+        v.bvh_nodes = c->bvh.nodes;
+        c->stats.bvh_nodes = (uint32_t)(ns - 1);
+        c->stats.accel_in_use = FORMA_RT_ACCEL_LBVH;
+    }
+    const size_t stage = (v.bvh_nodes ? 0 : spheres.size() * sizeof(float4)) + tris.size() * sizeof(float4);
+    v.smem_bytes = (!v.bvh_nodes && stage > 0 && stage <= (size_t)kSmemStageLimit) ? (int)stage : 0;
+
+    c->stats.n_objects = (uint32_t)n;
+    c->stats.n_spheres = ns; c->stats.n_planes = np; c->stats.n_triangles = nt;
+    c->scene_dirty = false;
+    return FORMA_RT_OK;
+}
+
+int ensure_scene(forma_rt* c) {
+    if (!c->scene_dirty) return FORMA_RT_OK;
+    return upload_scene(c);
+}
+
+}  // namespace
+
+// =====================================================================================================
+// C ABI
+// =====================================================================================================
+#define NEED_CTX(c) do { if (!(c)) return fail(FORMA_RT_EINVAL, "null forma_rt handle"); if ((c)->device >= 0) cudaSetDevice((c)->device); } while (0)
+// every entry point that touches the GPU: a host-only handle fails loudly, there is no CPU path
+#define NEED_DEV(c) do { NEED_CTX(c); if ((c)->device < 0) return fail(FORMA_RT_ECUDA, "handle was created with FORMA_RT_HOST_ONLY: no device, and there is no CPU fallback"); } while (0)
+
+extern "C" {
+
+const char* forma_rt_last_error(void) { return g_last_error.c_str(); }
+uint32_t forma_rt_abi_version(void) { return FORMA_RT_ABI_VERSION; }
+
+int forma_rt_create(const forma_rt_options* opts, uint32_t width, uint32_t height, forma_rt** out) {
+    if (!out) return fail(FORMA_RT_EINVAL, "forma_rt_create: out is null");
+    *out = nullptr;
+    if (width == 0 || height == 0 || (uint64_t)width * height > (1ull << 31))
+        return fail(FORMA_RT_EINVAL, "forma_rt_create: width/height out of range");
+    forma_rt_options o{};
+    o.struct_size = sizeof o;
+    if (opts) {
+        if (opts->struct_size != sizeof(forma_rt_options))
+            return fail(FORMA_RT_EINVAL, "forma_rt_create: options.struct_size mismatch (ABI skew)");
+        o = *opts;
+    }
+    if (o.accel > FORMA_RT_ACCEL_LBVH) return fail(FORMA_RT_EINVAL, "forma_rt_create: unknown accel");
+    if (o.flags & FORMA_RT_HOST_ONLY) {  // scene / camera bookkeeping only (tooling, CPU-side tests)
+        forma_rt* c = new (std::nothrow) forma_rt();
+        if (!c) return fail(FORMA_RT_ENOMEM, "forma_rt_create: out of host memory");
+        c->device = -1; c->width = width; c->height = height;
+        c->seed = o.seed; c->flags = o.flags; c->accel = o.accel;
+        c->scene.camera = forma::Camera::create(width, height);
+        c->scene.objects = forma::builtin_scene(0);
+        *out = c;
+        return FORMA_RT_OK;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(FORMA_RT_ECUDA, std::string("no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e));
+    if (o.device < 0 || o.device >= ndev) return fail(FORMA_RT_EINVAL, "forma_rt_create: device ordinal out of range");
+    CU_TRY(cudaSetDevice(o.device));
+
+    forma_rt* c = new (std::nothrow) forma_rt();
+    if (!c) return fail(FORMA_RT_ENOMEM, "forma_rt_create: out of host memory");
+    c->device = o.device; c->width = width; c->height = height;
+    c->seed = o.seed; c->flags = o.flags; c->accel = o.accel;
+    auto bail = [&](cudaError_t err, const char* what) {
+        delete c;
+        return fail(FORMA_RT_ECUDA, std::string(what) + ": " + cudaGetErrorString(err));
+    };
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    for (cudaEvent_t* ev : {&c->ev_begin, &c->ev_end, &c->ev_k0, &c->ev_k1})
+        if ((e = cudaEventCreate(ev)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaMalloc((void**)&c->d_rays, sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc");
+    if ((e = cudaMallocHost((void**)&c->h_rays, sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMallocHost");
+    cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, o.device);
+    cudaDeviceGetAttribute(&c->clock_khz, cudaDevAttrClockRate, o.device);
+    c->stats.sm_count = (uint32_t)c->sm_count;
+    c->stats.sm_clock_khz = (uint32_t)c->clock_khz;
+
+    // Scene::new (scene.rs:10-15): Camera::new + get_simple_scene
+    c->scene.camera = forma::Camera::create(width, height);
+    c->scene.objects = forma::builtin_scene(0);
+    c->scene_dirty = true;
+    *out = c;
+    return FORMA_RT_OK;
+}
+
+void forma_rt_destroy(forma_rt* ctx) { delete ctx; }
+
+int forma_rt_load_builtin(forma_rt* ctx, int which) {
+    NEED_CTX(ctx);
+    try {
+        ctx->scene.objects = forma::builtin_scene(which);
+    } catch (const std::exception& ex) {
+        return fail(FORMA_RT_EINVAL, ex.what());
+    }
+    ctx->scene_dirty = true;
+    return FORMA_RT_OK;
+}
+
+int forma_rt_load_json(forma_rt* ctx, const char* json, size_t len) {
+    NEED_CTX(ctx);
+    if (!json) return fail(FORMA_RT_EINVAL, "forma_rt_load_json: json is null");
+    try {
+        std::vector<forma_rt_object> objs;
+        forma::JsonCamera cam;
+        forma::load_json_scene(json, len, objs, cam);
+        ctx->scene.objects.swap(objs);
+        ctx->scene.json_camera = cam;
+    } catch (const std::exception& ex) {  // the reference panics here (scene_loader.rs:4 unwrap)
+        return fail(FORMA_RT_EJSON, ex.what());
+    }
+    ctx->scene_dirty = true;
+    return FORMA_RT_OK;
+}
+
+int forma_rt_load_objects(forma_rt* ctx, const forma_rt_object* objs, size_t n) {
+    NEED_CTX(ctx);
+    if (n && !objs) return fail(FORMA_RT_EINVAL, "forma_rt_load_objects: objs is null");
+    for (size_t i = 0; i < n; ++i)
+        if (objs[i].kind < FORMA_RT_SPHERE || objs[i].kind > FORMA_RT_TRIANGLE)
+            return fail(FORMA_RT_EINVAL, "forma_rt_load_objects: unknown object kind");
+    ctx->scene.objects.assign(objs, objs + n);
+    ctx->scene_dirty = true;
+    return FORMA_RT_OK;
+}
+
+int forma_rt_get_objects(forma_rt* ctx, forma_rt_object* objs, size_t cap, size_t* n) {
+    NEED_CTX(ctx);
+    const auto& v = ctx->scene.objects;
+    if (n) *n = v.size();
+    if (objs) std::memcpy(objs, v.data(), sizeof(forma_rt_object) * (cap < v.size() ? cap : v.size()));
+    return FORMA_RT_OK;
+}
+
+int forma_rt_set_object(forma_rt* ctx, uint32_t idx, const float* position, const float* orientation) {
+    NEED_CTX(ctx);
+    if (idx >= ctx->scene.objects.size()) return fail(FORMA_RT_EINVAL, "forma_rt_set_object: index out of range");
+    forma_rt_object& o = ctx->scene.objects[idx];
+    if (o.kind != FORMA_RT_PLANE) return FORMA_RT_OK;  // hitable.rs:12-13: default translate/rotate are no-ops
+    if (position) std::memcpy(o.a, position, 3 * sizeof(float));       // plane.rs:62-64: assigns
+    if (orientation) std::memcpy(o.b, orientation, 3 * sizeof(float)); // plane.rs:66-68: assigns
+    ctx->scene_dirty = true;
+    return FORMA_RT_OK;
+}
+
+// ---- camera ----------------------------------------------------------------------------------------
+int forma_rt_camera_new(forma_rt* ctx) {
+    NEED_CTX(ctx);
+    ctx->scene.camera = forma::Camera::create(ctx->width, ctx->height);
+    return FORMA_RT_OK;
+}
+
+int forma_rt_camera_look(forma_rt* ctx, const float from[3], const float at[3], const float up[3], float v_fov) {
+    NEED_CTX(ctx);
+    if (!from || !at || !up) return fail(FORMA_RT_EINVAL, "forma_rt_camera_look: null vector");
+    ctx->scene.camera = forma::Camera::look({from[0], from[1], from[2]}, {at[0], at[1], at[2]}, {up[0], up[1], up[2]},
+                                            v_fov, (float)ctx->width / (float)ctx->height);
+    return FORMA_RT_OK;
+}
+
+int forma_rt_camera_json(forma_rt* ctx) {
+    NEED_CTX(ctx);
+    const forma::JsonCamera& jc = ctx->scene.json_camera;
+    if (!jc.present) return fail(FORMA_RT_EINVAL, "forma_rt_camera_json: no JSON scene has been loaded");
+    // DESIGN.md "Scene mapping": forward = R*(0,0,1), up = R*(0,1,0), focus distance = |position|
+    forma::V3 ax, ay, az;
+    forma::quat_axes(jc.rotation, ax, ay, az);
+    float focus = forma::length(jc.position);
+    if (!(focus > 0.0f)) focus = 1.0f;
+    forma::V3 at{jc.position.x + focus * az.x, jc.position.y + focus * az.y, jc.position.z + focus * az.z};
+    ctx->scene.camera = forma::Camera::look(jc.position, at, ay, jc.fov, (float)ctx->width / (float)ctx->height);
+    return FORMA_RT_OK;
+}
+
+int forma_rt_camera_orbit(forma_rt* ctx, const float delta[3]) {
+    NEED_CTX(ctx);
+    if (!delta) return fail(FORMA_RT_EINVAL, "forma_rt_camera_orbit: null delta");
+    ctx->scene.camera.orbit({delta[0], delta[1], delta[2]});
+    return FORMA_RT_OK;
+}
+
+int forma_rt_camera_translate(forma_rt* ctx, const float delta[3]) {
+    NEED_CTX(ctx);
+    if (!delta) return fail(FORMA_RT_EINVAL, "forma_rt_camera_translate: null delta");
+    ctx->scene.camera.translate({delta[0], delta[1], delta[2]});
+    return FORMA_RT_OK;
+}
+
+int forma_rt_camera_get(forma_rt* ctx, forma_rt_camera* out) {
+    NEED_CTX(ctx);
+    if (!out) return fail(FORMA_RT_EINVAL, "forma_rt_camera_get: out is null");
+    *out = ctx->scene.camera.c;
+    return FORMA_RT_OK;
+}
+
+int forma_rt_camera_set(forma_rt* ctx, const forma_rt_camera* cam) {
+    NEED_CTX(ctx);
+    if (!cam) return fail(FORMA_RT_EINVAL, "forma_rt_camera_set: cam is null");
+    ctx->scene.camera.c = *cam;
+    return FORMA_RT_OK;
+}
+
+}  // extern "C"
+
+// ---- rendering ---------------------------------------------------------------------------------------
+namespace {
+
+// One launch of the trace kernel on `stream`; outputs are device pointers.  Records kernel events.
+int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t max_depth, uint32_t flags,
+                     uint8_t* d_rgb, float4* d_sum, cudaStream_t stream) {
+    if (spp == 0) return fail(FORMA_RT_EINVAL, "render: spp must be >= 1");
+    if (max_depth > (uint32_t)forma::kMaxDepthCap)
+        return fail(FORMA_RT_EINVAL, "render: max_depth exceeds the attenuation stack (64; the reference uses 50)");
+    int rc = ensure_scene(c);
+    if (rc) return rc;
+    forma::RenderParams P{};
+    P.cam = c->scene.camera.c;
+    P.scene = c->view;
+    P.width = c->width; P.height = c->height;
+    P.spp = spp; P.sample_offset = sample_offset; P.max_depth = max_depth; P.flags = flags;
+    P.key0 = (uint32_t)c->seed; P.key1 = (uint32_t)(c->seed >> 32);
+    P.rgb = d_rgb; P.sum = d_sum; P.rays = c->d_rays;
+    CU_TRY(cudaMemsetAsync(c->d_rays, 0, sizeof(unsigned long long), stream));
+    CU_TRY(cudaEventRecord(c->ev_k0, stream));
+    CU_TRY(forma::launch_render(P, stream));
+    CU_TRY(cudaEventRecord(c->ev_k1, stream));
+    c->stats.gpu_launches = 1;
+    c->stats.paths = (uint64_t)c->width * c->height * spp;
+    return FORMA_RT_OK;
+}
+
+// host-facing render: device buffers owned by the handle, D2H of what the caller asked for
+int render_to_host(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t max_depth, uint32_t flags,
+                   uint8_t* rgb, float* linear_rgba) {
+    const size_t npix = (size_t)c->width * c->height;
+    if (rgb) CU_TRY(c->d_rgb.ensure(npix * 3));
+    if (linear_rgba) CU_TRY(c->d_sum.ensure(npix));
+    cudaStream_t s = c->stream;
+    CU_TRY(cudaEventRecord(c->ev_begin, s));
+    int rc = render_on_device(c, spp, sample_offset, max_depth, flags, rgb ? c->d_rgb.p : nullptr,
+                              linear_rgba ? c->d_sum.p : nullptr, s);
+    if (rc) return rc;
+    if (rgb) CU_TRY(cudaMemcpyAsync(rgb, c->d_rgb.p, npix * 3, cudaMemcpyDeviceToHost, s));
+    if (linear_rgba) CU_TRY(cudaMemcpyAsync(linear_rgba, c->d_sum.p, npix * sizeof(float4), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaMemcpyAsync(c->h_rays, c->d_rays, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaEventRecord(c->ev_end, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    c->stats.rays = *c->h_rays;
+    CU_TRY(cudaEventElapsedTime(&c->stats.kernel_ms, c->ev_k0, c->ev_k1));
+    CU_TRY(cudaEventElapsedTime(&c->stats.total_ms, c->ev_begin, c->ev_end));
+    return FORMA_RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int forma_rt_render(forma_rt* ctx, uint32_t spp, uint32_t sample_offset, uint32_t max_depth, uint8_t* rgb,
+                    float* linear_rgba) {
+    NEED_DEV(ctx);
+    return render_to_host(ctx, spp, sample_offset, max_depth, ctx->flags, rgb, linear_rgba);
+}
+
+int forma_rt_update(forma_rt* ctx, uint8_t keys, float delta_time, uint8_t* rgb) {
+    NEED_DEV(ctx);
+    if (!rgb) return fail(FORMA_RT_EINVAL, "forma_rt_update: rgb is null");
+    ctx->scene.camera.orbit(forma::keys_to_delta(keys, delta_time));  // tracer.rs:31-52
+    int rc = render_to_host(ctx, 1, ctx->frame, 50, ctx->flags, rgb, nullptr);  // tracer.rs:54, MAX_DEPTH :10
+    if (rc == FORMA_RT_OK) ctx->frame++;
+    return rc;
+}
+
+int forma_rt_save_image(forma_rt* ctx, uint32_t sample, const char* path) {
+    NEED_DEV(ctx);
+    if (!path) return fail(FORMA_RT_EINVAL, "forma_rt_save_image: path is null");
+    std::vector<uint8_t> rgb((size_t)ctx->width * ctx->height * 3);
+    int rc = render_to_host(ctx, sample, 0, 50, ctx->flags, rgb.data(), nullptr);
+    if (rc) return rc;
+    return forma_rt_write_png(path, rgb.data(), ctx->width, ctx->height);
+}
+
+int forma_rt_primary_hits(forma_rt* ctx, int32_t* prim_id, float* t) {
+    NEED_DEV(ctx);
+    if (!prim_id || !t) return fail(FORMA_RT_EINVAL, "forma_rt_primary_hits: null output");
+    int rc = ensure_scene(ctx);
+    if (rc) return rc;
+    const size_t npix = (size_t)ctx->width * ctx->height;
+    CU_TRY(ctx->d_prim.ensure(npix));
+    CU_TRY(ctx->d_t.ensure(npix));
+    forma::PrimaryParams P{};
+    P.cam = ctx->scene.camera.c; P.scene = ctx->view;
+    P.width = ctx->width; P.height = ctx->height;
+    P.prim_id = ctx->d_prim.p; P.t = ctx->d_t.p;
+    cudaStream_t s = ctx->stream;
+    CU_TRY(cudaEventRecord(ctx->ev_begin, s));
+    CU_TRY(cudaEventRecord(ctx->ev_k0, s));
+    CU_TRY(forma::launch_primary_hits(P, s));
+    CU_TRY(cudaEventRecord(ctx->ev_k1, s));
+    CU_TRY(cudaMemcpyAsync(prim_id, ctx->d_prim.p, npix * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaMemcpyAsync(t, ctx->d_t.p, npix * sizeof(float), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaEventRecord(ctx->ev_end, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    ctx->stats.rays = npix; ctx->stats.paths = npix; ctx->stats.gpu_launches = 1;
+    CU_TRY(cudaEventElapsedTime(&ctx->stats.kernel_ms, ctx->ev_k0, ctx->ev_k1));
+    CU_TRY(cudaEventElapsedTime(&ctx->stats.total_ms, ctx->ev_begin, ctx->ev_end));
+    return FORMA_RT_OK;
+}
+
+// ---- device-resident entry points ----------------------------------------------------------------------
+int forma_rt_render_device(forma_rt* ctx, uint32_t spp, uint32_t sample_offset, uint32_t max_depth, void* d_rgb,
+                           void* d_sum_rgba, void* stream) {
+    NEED_DEV(ctx);
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    return render_on_device(ctx, spp, sample_offset, max_depth, ctx->flags, (uint8_t*)d_rgb, (float4*)d_sum_rgba, s);
+}
+
+int forma_rt_tonemap_device(forma_rt* ctx, const void* d_sum_rgba, uint32_t spp_total, uint64_t pixel_begin,
+                            uint64_t pixel_end, void* d_rgb, void* stream) {
+    NEED_DEV(ctx);
+    if (!d_sum_rgba || !d_rgb || spp_total == 0) return fail(FORMA_RT_EINVAL, "forma_rt_tonemap_device: bad argument");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    CU_TRY(forma::launch_tonemap((const float4*)d_sum_rgba, spp_total, pixel_begin, pixel_end, (uint8_t*)d_rgb,
+                                 ctx->sm_count, s));
+    return FORMA_RT_OK;
+}
+
+int forma_rt_reduce_tonemap_device(forma_rt* ctx, const void* const* d_peer_sums, uint32_t n_peers, uint32_t spp_total,
+                                   uint64_t pixel_begin, uint64_t pixel_end, void* d_rgb, void* d_sum_out,
+                                   void* stream) {
+    NEED_DEV(ctx);
+    if (!d_peer_sums || n_peers == 0 || spp_total == 0 || (!d_rgb && !d_sum_out))
+        return fail(FORMA_RT_EINVAL, "forma_rt_reduce_tonemap_device: bad argument");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    CU_TRY(forma::launch_reduce_tonemap((const float4* const*)d_peer_sums, (int)n_peers, spp_total, pixel_begin,
+                                        pixel_end, (uint8_t*)d_rgb, (float4*)d_sum_out, ctx->sm_count, s));
+    return FORMA_RT_OK;
+}
+
+int forma_rt_ipc_export(forma_rt* ctx, void* d_ptr, uint8_t handle[64]) {
+    NEED_DEV(ctx);
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    cudaIpcMemHandle_t h;
+    CU_TRY(cudaIpcGetMemHandle(&h, d_ptr));
+    std::memcpy(handle, &h, 64);
+    return FORMA_RT_OK;
+}
+
+int forma_rt_ipc_open(forma_rt* ctx, const uint8_t handle[64], void** d_ptr) {
+    NEED_DEV(ctx);
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, 64);
+    CU_TRY(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return FORMA_RT_OK;
+}
+
+int forma_rt_ipc_close(forma_rt* ctx, void* d_ptr) {
+    NEED_DEV(ctx);
+    CU_TRY(cudaIpcCloseMemHandle(d_ptr));
+    return FORMA_RT_OK;
+}
+
+int forma_rt_device_alloc(forma_rt* ctx, size_t bytes, void** d_ptr) {
+    NEED_DEV(ctx);
+    if (!d_ptr) return fail(FORMA_RT_EINVAL, "forma_rt_device_alloc: d_ptr is null");
+    CU_TRY(cudaMalloc(d_ptr, bytes ? bytes : 1));
+    ctx->scratch.push_back(*d_ptr);
+    return FORMA_RT_OK;
+}
+
+int forma_rt_device_free(forma_rt* ctx, void* d_ptr) {
+    NEED_DEV(ctx);
+    for (size_t i = 0; i < ctx->scratch.size(); ++i)
+        if (ctx->scratch[i] == d_ptr) {
+            ctx->scratch.erase(ctx->scratch.begin() + i);
+            CU_TRY(cudaFree(d_ptr));
+            return FORMA_RT_OK;
+        }
+    return fail(FORMA_RT_EINVAL, "forma_rt_device_free: pointer not owned by this handle");
+}
+
+int forma_rt_synchronize(forma_rt* ctx) {
+    NEED_DEV(ctx);
+    CU_TRY(cudaStreamSynchronize(ctx->stream));
+    return FORMA_RT_OK;
+}
+
+int forma_rt_stats_get(forma_rt* ctx, forma_rt_stats* out) {
+    NEED_CTX(ctx);
+    if (!out) return fail(FORMA_RT_EINVAL, "forma_rt_stats_get: out is null");
+    *out = ctx->stats;
+    return FORMA_RT_OK;
+}
+
+int forma_rt_write_png(const char* path, const uint8_t* rgb, uint32_t width, uint32_t height) {
+    std::string err;
+    if (!forma::write_png_rgb8(path, rgb, width, height, err)) return fail(FORMA_RT_EIO, err);
+    return FORMA_RT_OK;
+}
+
+}  // extern "C"

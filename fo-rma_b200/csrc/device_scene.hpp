@@ -1,0 +1,74 @@
+// device_scene.hpp — how Scene.objects (cpu_ray_tracer/scene.rs:4-7) is laid out in HBM, and the
+// kernel parameter blocks.  Shared by the host packer (context.cu) and the kernels (trace.cuh).
+//
+// The reference scans a Vec<Box<dyn Hitable>> in list order with one shared HitRecord
+// (tracer.rs:190-200).  Only Plane::hit is order-sensitive (it ignores t_max for t and clobbers the
+// record, plane.rs:25-41), so the list is cut into SEGMENTS at every plane: inside a segment the
+// spheres and triangles are order-independent up to the tie rule "equal t keeps the earlier list
+// entry", and are stored type-sorted as float4 SoA:
+//
+//   spheres[i]      = (cx, cy, cz, r)                                  16 B
+//   tris[3i..3i+2]  = (v0 | n.x), (e1 | n.y), (e2 | n.z)               48 B   e1 = v1-v0, e2 = v2-v0,
+//                                                                      n = unit(cross(e1,e2)), host f32
+//   planes[3k..3k+2]= position, orientation, size (w unused)            48 B
+//   *_obj[i]        = list index of packed primitive i (ties, material lookup)
+//   material[j]     = (r, g, b, fuzz) of list entry j                  16 B
+//   kindmat[j]      = kind | material << 8;  ids[j] = reported id
+//   segments[s]     = (sph_begin, sph_end, tri_begin, tri_end, plane)  plane = -1 when none follows
+//
+// With accel = LBVH the spheres of the (single) segment are additionally indexed by a binary
+// radix tree (lbvh.cu): bvh_nodes[2k], [2k+1] = child boxes of internal node k.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/forma_rt.h"
+
+namespace forma {
+
+constexpr int kMaxDepthCap = 64;  // size of the per-path attenuation stack (reference: MAX_DEPTH 50)
+
+struct Segment {
+    int sph_begin, sph_end, tri_begin, tri_end, plane;
+};
+
+struct SceneView {
+    const float4* spheres;
+    const int* sphere_obj;
+    const float4* tris;
+    const int* tri_obj;
+    const float4* planes;
+    const int* plane_obj;
+    const Segment* segments;
+    const float4* material;
+    const int* kindmat;
+    const int* ids;
+    // LBVH over spheres[0 .. n_spheres) (nullptr = brute force)
+    const float4* bvh_nodes;   // 4 float4 per internal node: see lbvh.cu
+    int n_segments;
+    int n_spheres;
+    int n_tris;
+    int n_planes;
+    int smem_bytes;            // > 0: spheres+tris are staged in shared memory by the kernel
+};
+
+struct RenderParams {
+    forma_rt_camera cam;
+    SceneView scene;
+    uint32_t width, height;
+    uint32_t spp, sample_offset, max_depth, flags;
+    uint32_t key0, key1;       // Philox key = seed
+    uint8_t* rgb;              // nullable
+    float4* sum;               // nullable
+    unsigned long long* rays;  // device counter
+};
+
+struct PrimaryParams {
+    forma_rt_camera cam;
+    SceneView scene;
+    uint32_t width, height;
+    int32_t* prim_id;
+    float* t;
+};
+
+}  // namespace forma

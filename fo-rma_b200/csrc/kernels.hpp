@@ -1,0 +1,16 @@
+// kernels.hpp — launchers exported by kernels.cu / lbvh.cu to the context (context.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "device_scene.hpp"
+
+namespace forma {
+
+cudaError_t launch_render(const RenderParams& P, cudaStream_t stream);
+cudaError_t launch_primary_hits(const PrimaryParams& P, cudaStream_t stream);
+cudaError_t launch_tonemap(const float4* sum, uint32_t spp, uint64_t begin, uint64_t end, uint8_t* rgb, int sm_count,
+                           cudaStream_t stream);
+cudaError_t launch_reduce_tonemap(const float4* const* peers, int n_peers, uint32_t spp, uint64_t begin, uint64_t end,
+                                  uint8_t* rgb, float4* sum_out, int sm_count, cudaStream_t stream);
+
+}  // namespace forma

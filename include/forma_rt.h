@@ -1,0 +1,193 @@
+/* forma_rt.h — C ABI of libforma_rt.so, the B200 (sm_100a) drop-in for the per-pixel path-tracing
+ * loop of fo-rma's `src/cpu_ray_tracer` (reference paths below are relative to the fo-rma tree).
+ *
+ * The reference has no FFI layer of its own (no `extern`, `#[no_mangle]` or cdylib): its boundary
+ * is the four public Rust functions of cpu_ray_tracer/tracer.rs plus Scene / Camera / Hitable and
+ * the JSON loader.  Each entry point below names the reference interface it replaces; a thin Rust
+ * crate keeps the Rust names and signatures and forwards to these symbols.
+ *
+ * Conventions: every call returns 0 on success and a negative FORMA_RT_E* code on failure;
+ * forma_rt_last_error() returns a thread-local NUL-terminated message for the last failure on the
+ * calling thread (the reference panics instead: tracer.rs:157,186, scene_loader.rs:4).  The caller
+ * owns every host buffer; the library owns all device memory.  A handle is used from one host
+ * thread at a time (the reference has a single caller, frontend/macroquad.rs:14-92).  There is no
+ * CPU fallback: without a usable CUDA device forma_rt_create fails with FORMA_RT_ECUDA.
+ */
+#ifndef FORMA_RT_H
+#define FORMA_RT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define FORMA_RT_API __attribute__((visibility("default")))
+#else
+#define FORMA_RT_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FORMA_RT_ABI_VERSION 1
+
+/* error codes */
+#define FORMA_RT_OK 0
+#define FORMA_RT_EINVAL (-1)  /* bad argument / state (e.g. render before a camera exists) */
+#define FORMA_RT_EJSON (-2)   /* scene JSON does not parse or lacks a required field */
+#define FORMA_RT_ECUDA (-3)   /* CUDA runtime error, or no device */
+#define FORMA_RT_EIO (-4)     /* file could not be written */
+#define FORMA_RT_ENOMEM (-5)
+
+/* forma_rt_options.flags */
+#define FORMA_RT_NO_JITTER 1u /* xi_u = xi_v = 0.5 instead of tracer.rs:66-67's two draws (added mode) */
+#define FORMA_RT_PINHOLE 2u   /* skip camera.rs:63-64's lens sample: offset = 0 (added mode) */
+#define FORMA_RT_HOST_ONLY 4u /* no device: scene/camera bookkeeping only; every render call fails with FORMA_RT_ECUDA */
+
+/* forma_rt_options.accel */
+#define FORMA_RT_ACCEL_AUTO 0u  /* brute-force scan below FORMA_RT_BVH_THRESHOLD spheres, LBVH above */
+#define FORMA_RT_ACCEL_BRUTE 1u /* tracer.rs:195-200's linear scan, as-is */
+#define FORMA_RT_ACCEL_LBVH 2u  /* on-GPU Morton-code LBVH over the spheres (reference has none: aabb.rs is a stub) */
+
+/* forma_rt_object.kind — one record per entry of Scene.objects (cpu_ray_tracer/scene.rs:4-7) */
+#define FORMA_RT_SPHERE 0   /* shapes/sphere.rs:8-14 */
+#define FORMA_RT_PLANE 1    /* shapes/plane.rs:8-15  */
+#define FORMA_RT_TRIANGLE 2 /* extension for the JSON mesh names; no reference counterpart */
+
+typedef struct forma_rt forma_rt; /* opaque: TraceModel (tracer.rs:12-17) + its device mirror */
+
+typedef struct forma_rt_options {
+    uint32_t struct_size; /* = sizeof(forma_rt_options) */
+    int32_t device;       /* CUDA device ordinal */
+    uint64_t seed;        /* Philox key; the reference's thread_rng is OS-seeded (utility.rs:5) */
+    uint32_t flags;       /* FORMA_RT_NO_JITTER | FORMA_RT_PINHOLE | FORMA_RT_HOST_ONLY */
+    uint32_t accel;       /* FORMA_RT_ACCEL_* */
+} forma_rt_options;
+
+/* 64 bytes; the flat form of a `Box<dyn Hitable>` (shapes/hitable.rs:4-14). */
+typedef struct forma_rt_object {
+    int32_t kind;     /* FORMA_RT_SPHERE | PLANE | TRIANGLE */
+    int32_t material; /* sphere.rs:60-70: 0 lambertian, 1 metal, 2 dielectric, 3 "light", other lambertian */
+    int32_t id;       /* what forma_rt_primary_hits reports for this object */
+    float fuzz;
+    float color[3];
+    float a[3]; /* sphere center        | plane position    | triangle v0 */
+    float b[3]; /* sphere (radius,0,0)  | plane orientation | triangle v1 */
+    float c[3]; /* unused               | plane size        | triangle v2 */
+} forma_rt_object;
+
+/* cpu_ray_tracer/camera.rs:7-21, same field order; 26 floats */
+typedef struct forma_rt_camera {
+    float position[3];
+    float lower_left_corner[3];
+    float aspect;
+    float horizontal[3];
+    float vertical[3];
+    float u[3], v[3], w[3];
+    float lens_radius;
+    float focus_dist;
+    float radius;
+    float rotation;
+} forma_rt_camera;
+
+typedef struct forma_rt_stats {
+    uint64_t rays;          /* closest-hit queries (get_color calls, tracer.rs:189) of the last render call */
+    uint64_t paths;         /* (pixel, sample) pairs of the last render call */
+    float kernel_ms;        /* CUDA-event time of the trace kernel(s) of the last render call */
+    float total_ms;         /* CUDA-event time of the whole call on the device stream, copies included */
+    uint32_t gpu_launches;  /* kernels launched by the last render call */
+    uint32_t n_objects, n_spheres, n_planes, n_triangles;
+    uint32_t bvh_nodes;     /* 0 when the brute-force scan is in use */
+    uint32_t accel_in_use;  /* FORMA_RT_ACCEL_BRUTE | FORMA_RT_ACCEL_LBVH */
+    uint32_t sm_count;
+    uint32_t sm_clock_khz;  /* cudaDevAttrClockRate */
+} forma_rt_stats;
+
+/* ---- life cycle ------------------------------------------------------------------------------ */
+/* tracer::create_model (tracer.rs:19-28): width x height model with Scene::new's content
+ * (scene.rs:10-15: Camera::new + scenes::get_simple_scene). */
+FORMA_RT_API int forma_rt_create(const forma_rt_options* opts, uint32_t width, uint32_t height, forma_rt** out);
+FORMA_RT_API void forma_rt_destroy(forma_rt* ctx);
+FORMA_RT_API const char* forma_rt_last_error(void);
+FORMA_RT_API uint32_t forma_rt_abi_version(void);
+
+/* ---- scene: Scene.objects (scene.rs:4-7) ------------------------------------------------------ */
+/* scenes.rs: 0 get_simple_scene (:6-39), 1 get_plane_scene (:41-113), 2 get_objects (:115-156) */
+FORMA_RT_API int forma_rt_load_builtin(forma_rt* ctx, int which);
+/* scene_loader::construct_scene_from_json (basics/scene_loader.rs:3-7), schema :9-66, plus the
+ * JSON -> ray-traceable mapping (DESIGN.md "Scene mapping"; optional per-object "rt" block).
+ * Also records the JSON camera for forma_rt_camera_json.  Unknown keys are ignored (serde default). */
+FORMA_RT_API int forma_rt_load_json(forma_rt* ctx, const char* json, size_t len);
+/* replace Scene.objects by an explicit list */
+FORMA_RT_API int forma_rt_load_objects(forma_rt* ctx, const forma_rt_object* objs, size_t n);
+/* read Scene.objects back: *n = count; copies min(*n, cap) records when objs != NULL */
+FORMA_RT_API int forma_rt_get_objects(forma_rt* ctx, forma_rt_object* objs, size_t cap, size_t* n);
+/* Hitable::translate / Hitable::rotate on objects[idx] (hitable.rs:12-13, plane.rs:62-68; the
+ * frontend calls both on objects[0] every frame, macroquad.rs:66-67).  Planes ASSIGN position /
+ * orientation; every other kind ignores the call, as in the reference.  NULL = leave unchanged. */
+FORMA_RT_API int forma_rt_set_object(forma_rt* ctx, uint32_t idx, const float* position, const float* orientation);
+
+/* ---- camera: Scene.camera (camera.rs) --------------------------------------------------------- */
+FORMA_RT_API int forma_rt_camera_new(forma_rt* ctx);  /* Camera::new(width, height), camera.rs:24-60 */
+/* Camera::new's arithmetic for an arbitrary look-at (added; used by the JSON camera) */
+FORMA_RT_API int forma_rt_camera_look(forma_rt* ctx, const float from[3], const float at[3], const float up[3], float v_fov);
+FORMA_RT_API int forma_rt_camera_json(forma_rt* ctx);                          /* camera of the last load_json (added) */
+FORMA_RT_API int forma_rt_camera_orbit(forma_rt* ctx, const float delta[3]);     /* Camera::orbit, camera.rs:97-122 */
+FORMA_RT_API int forma_rt_camera_translate(forma_rt* ctx, const float delta[3]); /* Camera::translate, camera.rs:74-95 */
+FORMA_RT_API int forma_rt_camera_get(forma_rt* ctx, forma_rt_camera* out);
+FORMA_RT_API int forma_rt_camera_set(forma_rt* ctx, const forma_rt_camera* cam);
+
+/* ---- rendering -------------------------------------------------------------------------------- */
+/* tracer::update (tracer.rs:30-55): keys = 00EQADWS, orbit the camera, then one 1-spp frame
+ * (render, tracer.rs:57-81) into rgb[width*height*3] (RGB8, row-major, row 0 = top).
+ * Frame k of a handle uses sample index k so successive frames are decorrelated. */
+FORMA_RT_API int forma_rt_update(forma_rt* ctx, uint8_t keys, float delta_time, uint8_t* rgb);
+/* tracer::save_image's loops (tracer.rs:168-184) without the PNG write: spp samples per pixel,
+ * sample indices sample_offset .. sample_offset+spp-1, paths up to max_depth scatters
+ * (tracer.rs:10: 50).  rgb (nullable): width*height*3 sqrt-gamma bytes of sum/spp.
+ * linear_rgba (nullable): width*height*4 floats, the per-pixel f32 SUM over the samples in sample
+ * order (r,g,b) and the sample count in .a. */
+FORMA_RT_API int forma_rt_render(forma_rt* ctx, uint32_t spp, uint32_t sample_offset, uint32_t max_depth, uint8_t* rgb,
+                    float* linear_rgba);
+/* tracer::save_image (tracer.rs:160-187): forma_rt_render + PNG to `path` ("out/basic.png" in the
+ * reference).  Fails with FORMA_RT_EIO where the reference panics. */
+FORMA_RT_API int forma_rt_save_image(forma_rt* ctx, uint32_t sample, const char* path);
+/* primary-ray dump (added; config B): xi = 0.5, pinhole.  prim_id[width*height] = object id of the
+ * closest hit or -1; t[width*height] = its distance (FLT_MAX on a miss). */
+FORMA_RT_API int forma_rt_primary_hits(forma_rt* ctx, int32_t* prim_id, float* t);
+
+/* ---- device-resident entry points (one process per GPU; torch.distributed moves the buffers) --- */
+/* Same as forma_rt_render but the outputs are DEVICE pointers on ctx's device and nothing is copied
+ * to the host; runs on `stream` (a cudaStream_t, NULL = the handle's own stream) without
+ * synchronising it.  d_sum_rgba: width*height float4 (nullable).  d_rgb: width*height*3 bytes (nullable). */
+FORMA_RT_API int forma_rt_render_device(forma_rt* ctx, uint32_t spp, uint32_t sample_offset, uint32_t max_depth, void* d_rgb,
+                           void* d_sum_rgba, void* stream);
+/* tracer.rs:177-184 on a summed buffer: rgb = as_u8(sqrt(sum / spp_total) * 255), pixels
+ * [pixel_begin, pixel_end).  Used after the cross-GPU reduce of the per-rank sums. */
+FORMA_RT_API int forma_rt_tonemap_device(forma_rt* ctx, const void* d_sum_rgba, uint32_t spp_total, uint64_t pixel_begin,
+                            uint64_t pixel_end, void* d_rgb, void* stream);
+/* Fused exchange step for the sample-split: for pixels [pixel_begin, pixel_end) sum the n_peers
+ * float4 buffers (device pointers that may live on peer GPUs, mapped through CUDA IPC / P2P) in rank
+ * order and tone-map in the same kernel — the reduce and the write-out never round-trip HBM. */
+FORMA_RT_API int forma_rt_reduce_tonemap_device(forma_rt* ctx, const void* const* d_peer_sums, uint32_t n_peers,
+                                   uint32_t spp_total, uint64_t pixel_begin, uint64_t pixel_end, void* d_rgb,
+                                   void* d_sum_out, void* stream);
+/* CUDA IPC plumbing for the above: export a handle (64 bytes) of a device allocation of this
+ * process, open a peer's handle, close it. */
+FORMA_RT_API int forma_rt_ipc_export(forma_rt* ctx, void* d_ptr, uint8_t handle[64]);
+FORMA_RT_API int forma_rt_ipc_open(forma_rt* ctx, const uint8_t handle[64], void** d_ptr);
+FORMA_RT_API int forma_rt_ipc_close(forma_rt* ctx, void* d_ptr);
+/* scratch device allocations owned by the handle (freed by forma_rt_destroy) */
+FORMA_RT_API int forma_rt_device_alloc(forma_rt* ctx, size_t bytes, void** d_ptr);
+FORMA_RT_API int forma_rt_device_free(forma_rt* ctx, void* d_ptr);
+FORMA_RT_API int forma_rt_synchronize(forma_rt* ctx);
+
+/* ---- misc -------------------------------------------------------------------------------------- */
+FORMA_RT_API int forma_rt_stats_get(forma_rt* ctx, forma_rt_stats* out);
+/* RGB8 -> PNG file (the `image` crate's role at tracer.rs:186) */
+FORMA_RT_API int forma_rt_write_png(const char* path, const uint8_t* rgb, uint32_t width, uint32_t height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FORMA_RT_H */
