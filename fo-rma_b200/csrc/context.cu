@@ -65,6 +65,7 @@ struct forma_rt {
     uint32_t flags = 0, accel = FORMA_RT_ACCEL_AUTO;
     forma::Scene scene;
     bool scene_dirty = true;
+    bool stats_pending = false;
     uint32_t frame = 0;  // update() call counter -> sample index of the interactive frame
 
     // packed scene (host copies kept for re-upload after set_object)
@@ -418,7 +419,7 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
     P.scene = c->view;
     P.width = c->width; P.height = c->height;
     P.spp = spp; P.sample_offset = sample_offset; P.max_depth = max_depth; P.flags = flags;
-    P.key0 = (uint32_t)c->seed; P.key1 = (uint32_t)(c->seed >> 32);
+    P.rk.expand(c->seed);
     P.rgb = d_rgb; P.sum = d_sum; P.rays = c->d_rays;
     CU_TRY(cudaMemsetAsync(c->d_rays, 0, sizeof(unsigned long long), stream));
     CU_TRY(cudaEventRecord(c->ev_k0, stream));
@@ -426,6 +427,7 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
     CU_TRY(cudaEventRecord(c->ev_k1, stream));
     c->stats.gpu_launches = 1;
     c->stats.paths = (uint64_t)c->width * c->height * spp;
+    c->stats_pending = true;  // ray counter + kernel time are read back by whoever synchronises
     return FORMA_RT_OK;
 }
 
@@ -446,6 +448,7 @@ int render_to_host(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t m
     CU_TRY(cudaEventRecord(c->ev_end, s));
     CU_TRY(cudaStreamSynchronize(s));
     c->stats.rays = *c->h_rays;
+    c->stats_pending = false;
     CU_TRY(cudaEventElapsedTime(&c->stats.kernel_ms, c->ev_k0, c->ev_k1));
     CU_TRY(cudaEventElapsedTime(&c->stats.total_ms, c->ev_begin, c->ev_end));
     return FORMA_RT_OK;
@@ -587,6 +590,15 @@ int forma_rt_synchronize(forma_rt* ctx) {
 int forma_rt_stats_get(forma_rt* ctx, forma_rt_stats* out) {
     NEED_CTX(ctx);
     if (!out) return fail(FORMA_RT_EINVAL, "forma_rt_stats_get: out is null");
+    if (ctx->stats_pending && ctx->device >= 0) {  // a forma_rt_render_device launch has not been read back yet
+        CU_TRY(cudaEventSynchronize(ctx->ev_k1));
+        CU_TRY(cudaMemcpyAsync(ctx->h_rays, ctx->d_rays, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+        CU_TRY(cudaStreamSynchronize(ctx->stream));
+        ctx->stats.rays = *ctx->h_rays;
+        CU_TRY(cudaEventElapsedTime(&ctx->stats.kernel_ms, ctx->ev_k0, ctx->ev_k1));
+        ctx->stats.total_ms = ctx->stats.kernel_ms;
+        ctx->stats_pending = false;
+    }
     *out = ctx->stats;
     return FORMA_RT_OK;
 }

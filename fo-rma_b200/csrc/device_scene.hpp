@@ -52,12 +52,21 @@ struct SceneView {
     int smem_bytes;            // > 0: spheres+tris are staged in shared memory by the kernel
 };
 
+// Philox4x32-10 round keys: k[2r], k[2r+1] = (seed_lo + r*0x9E3779B9, seed_hi + r*0xBB67AE85)
+struct RoundKeys {
+    uint32_t k[20];
+    void expand(uint64_t seed) {
+        uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+        for (int r = 0; r < 10; ++r) { k[2 * r] = k0; k[2 * r + 1] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+    }
+};
+
 struct RenderParams {
     forma_rt_camera cam;
     SceneView scene;
     uint32_t width, height;
     uint32_t spp, sample_offset, max_depth, flags;
-    uint32_t key0, key1;       // Philox key = seed
+    RoundKeys rk;              // Philox key schedule of the seed
     uint8_t* rgb;              // nullable
     float4* sum;               // nullable
     unsigned long long* rays;  // device counter

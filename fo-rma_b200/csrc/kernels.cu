@@ -46,9 +46,7 @@ __global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ 
     uint32_t rays = 0;
     float3 col = f3(0.0f, 0.0f, 0.0f);
     if (live) {
-        PathRng rng;
-        rng.k0 = P.key0; rng.k1 = P.key1;
-        rng.pixel = x + y * P.width;
+        PathRng rng{P.rk, x + y * P.width, 0u};
         const float fx = (float)x, fy = (float)(P.height - y);  // tracer.rs:171-172 (Q1: height - y)
         const float fw = (float)P.width, fh = (float)P.height;
         const bool no_jitter = P.flags & FORMA_RT_NO_JITTER, pinhole = P.flags & FORMA_RT_PINHOLE;
@@ -102,7 +100,8 @@ __global__ void __launch_bounds__(kBlock) primary_hits_kernel(const __grid_const
     if (x >= P.width || y >= P.height) return;
     const float u = ((float)x + 0.5f) / (float)P.width;
     const float v = ((float)(P.height - y) + 0.5f) / (float)P.height;
-    PathRng rng{0, 0, 0, 0};
+    const RoundKeys no_keys{};
+    PathRng rng{no_keys, 0u, 0u};
     Rand4 r0{0.5f, 0.5f, 0.0f, 0.0f};
     float3 o, d;
     camera_ray(P.cam, rng, r0, u, v, true, o, d);

@@ -33,17 +33,17 @@ __device__ __forceinline__ float3 unit(float3 a) { return a / length(a); }
 struct Rand4 {
     float x, y, z, w;
 };
-__device__ __forceinline__ Rand4 philox_unit4(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t c2,
-                                              uint32_t c3) {
+// Round keys k + r*W are the same for every call of a launch, so the host expands them once
+// (RoundKeys, device_scene.hpp) and the kernel reads them as constant-bank operands: a round is
+// two IMAD.WIDE (hi and lo of each product in one instruction) and two 3-input LOP3.
+__device__ __forceinline__ Rand4 philox_unit4(const RoundKeys& rk, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
-        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-        uint32_t n0 = hi1 ^ c1 ^ k0;
-        uint32_t n2 = hi0 ^ c3 ^ k1;
-        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
-        k0 += 0x9E3779B9u;
-        k1 += 0xBB67AE85u;
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+        const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ rk.k[2 * r];
+        const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ rk.k[2 * r + 1];
+        c1 = (uint32_t)p1; c3 = (uint32_t)p0; c0 = n0; c2 = n2;
     }
     const float s = 1.0f / 16777216.0f;
     Rand4 o;
@@ -55,9 +55,10 @@ __device__ __forceinline__ Rand4 philox_unit4(uint32_t k0, uint32_t k1, uint32_t
 }
 
 struct PathRng {
-    uint32_t k0, k1, pixel, sample;
+    const RoundKeys& rk;
+    uint32_t pixel, sample;
     __device__ __forceinline__ Rand4 block(uint32_t slot, uint32_t blk) const {
-        return philox_unit4(k0, k1, pixel, sample, slot, blk);
+        return philox_unit4(rk, pixel, sample, slot, blk);
     }
 };
 

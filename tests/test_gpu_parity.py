@@ -1,0 +1,161 @@
+"""GPU parity tests proper (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle
+on the same seeded inputs.  Bar: BIT-EXACT — hit ids, hit distance t, per-pixel f32 sums, RGB8
+bytes and the ray count (the GPU build uses -fmad=false / IEEE div+sqrt, the oracle
+-ffp-contract=off, and both use the same counter-based Philox stream)."""
+import os
+
+import numpy as np
+import pytest
+
+import forma_b200
+from forma_b200 import _lib
+from oracle import binding as ob
+from oracle.scene_oracle import OBJECT_DTYPE
+
+from conftest import load_scene_pair
+from test_oracle_analytic import plane, sphere, tri
+
+pytestmark = pytest.mark.gpu
+NT = os.cpu_count() or 1
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def assert_render_equal(m, objs, cam, w, h, spp, seed, **kw):
+    rgb_o, lin_o, rays_o = ob.render(objs, cam, w, h, spp, seed=seed, nthreads=NT, **kw)
+    rgb_g, lin_g = m.render(spp, want_linear=True, **{k: v for k, v in kw.items() if k != "flags"})
+    st = m.stats()
+    assert st.rays == rays_o and st.paths == w * h * spp and st.gpu_launches >= 1
+    assert np.array_equal(bits(lin_g[..., :3]), bits(lin_o)), "per-pixel f32 sums differ"
+    assert (lin_g[..., 3] == spp).all()
+    assert np.array_equal(rgb_g, rgb_o)
+
+
+@pytest.mark.parametrize("which,w,h,spp", [(0, 200, 120, 6), (2, 200, 120, 6), (2, 67, 45, 3), (1, 64, 32, 2)])
+def test_builtin_scenes_bit_exact(which, w, h, spp):
+    m = forma_b200.create_model(w, h, seed=1234 + which)
+    m.scene.load_builtin(which)
+    assert_render_equal(m, ob.builtin_scene(which), ob.camera_new(w, h), w, h, spp, 1234 + which)
+
+
+def test_reference_frontend_sequence_bit_exact():
+    """macroquad.rs:12-13,66-68: translate/rotate objects[0] (the plane becomes live), update() orbits."""
+    w, h = 160, 96
+    m = forma_b200.create_model(w, h, seed=9)
+    objs, cam = ob.builtin_scene(0), ob.camera_new(w, h)
+    for frame, keys in enumerate([0, 0b001000, 0b010010]):
+        m.scene.objects[0].translate((-1.0, 0.0, 0.0)); m.scene.objects[0].rotate((-1.0, 0.0, 0.0))
+        objs["a"][0] = (-1.0, 0.0, 0.0); objs["b"][0] = (-1.0, 0.0, 0.0)
+        forma_b200.update(m, keys, 0.125)
+        ob.update_camera(cam, keys, 0.125)
+        assert np.array_equal(bits(m.scene.camera.as_array()), bits(cam))
+        rgb_o, _, _ = ob.render(objs, cam, w, h, 1, sample_offset=frame, seed=9, nthreads=NT)
+        assert np.array_equal(m.pixels.reshape(h, w, 3), rgb_o)
+        assert (rgb_o[..., 0] > rgb_o[..., 2] + 40).any()  # the red metal plane is in view
+
+
+@pytest.mark.parametrize("name,w,h,spp", [("scene_09", 320, 180, 8), ("scene_01", 160, 90, 2), ("scene_05", 128, 72, 1),
+                                          ("scene_02", 96, 54, 2), ("scene_06", 96, 54, 1), ("scene_07", 64, 36, 2)])
+def test_json_scenes_bit_exact(name, w, h, spp):
+    txt, objs, cam = load_scene_pair(name, w, h)
+    m = forma_b200.create_model(w, h, seed=42)
+    m.scene.load_json(txt)
+    m.scene.camera.use_json()
+    assert_render_equal(m, objs, cam, w, h, spp, 42)
+
+
+def test_config_b_primary_hits_full_size():
+    """BASELINE config B: scene_05 at 1920x1080, un-jittered pinhole primary rays: ids bit-exact,
+    t bit-exact (the bar was 1e-4 relative)."""
+    w, h = 1920, 1080
+    txt, objs, cam = load_scene_pair("scene_05", w, h)
+    m = forma_b200.create_model(w, h)
+    m.scene.load_json(txt)
+    m.scene.camera.use_json()
+    ids_g, t_g = m.primary_hits()
+    ids_o, t_o = ob.primary_hits(objs, cam, w, h)
+    assert np.array_equal(ids_g, ids_o) and np.array_equal(bits(t_g), bits(t_o))
+    hit = ids_g >= 0
+    assert 0.3 < hit.mean() <= 1.0 and len(np.unique(ids_g[hit] >> 16)) > 30
+    assert (t_g[~hit] == np.finfo(np.float32).max).all()
+    # a frame that also contains misses: the built-in camera looks past the scene
+    m.scene.camera.reset()
+    ids2, t2 = m.primary_hits()
+    ids2_o, t2_o = ob.primary_hits(objs, ob.camera_new(w, h), w, h)
+    assert np.array_equal(ids2, ids2_o) and np.array_equal(bits(t2), bits(t2_o))
+    assert (t2[ids2 < 0] == np.finfo(np.float32).max).all()
+
+
+def test_mixed_list_order_semantics():
+    """Planes between spheres and triangles: segment boundaries, the Q5 record clobber, ties on equal t
+    (earlier list entry wins), a negative-t plane accept that blocks everything after it."""
+    rng = np.random.default_rng(5)
+    objs = [sphere((0, 0, -3), 1.0, mat=0, col=(.8, .3, .3), id=10),
+            plane((0, 0, -2.5), (0, 0, -1), (0.6, 0.6, 5), mat=1, col=(.9, .9, .9), id=11),   # in front of sphere 10
+            tri((-3, -1, -4), (3, -1, -4), (0, 3, -4), id=12),
+            sphere((0, 0, -3), 1.0, mat=1, col=(.1, .9, .1), fuzz=0.3, id=13),                # coincident with 10: loses ties
+            plane((5, 0, -2), (0, 0, -1), (0.5, 0.5, 5), mat=0, col=(.2, .2, .9), id=14),     # extent-rejects: clobbers t,p
+            tri((-3, -1, -4), (3, -1, -4), (0, 3, -4), id=15),                                 # coincident with 12: loses
+            sphere((1.5, 0.5, -2), 0.4, mat=2, col=(.9, .9, .9), id=16),
+            plane((0, -1.2, 3), (0, 0.2, -1), (0.5, 9, 9), mat=0, col=(.5, .5, .1), id=17),    # behind the eye: negative t
+            sphere((-1.5, 0.5, -2), 0.4, mat=3, col=(.1, .1, .1), id=18)]
+    for _ in range(6):
+        c = rng.uniform(-2, 2, 3); c[2] -= 4
+        objs.append(sphere(c, rng.uniform(.2, .6), mat=int(rng.integers(0, 5)), col=rng.uniform(.1, .9, 3),
+                           fuzz=rng.uniform(0, 1), id=100 + _))
+    objs = np.stack(objs)
+    w, h = 96, 64
+    m = forma_b200.create_model(w, h, seed=77)
+    m.scene.load_objects(objs)
+    cam = ob.camera_new(w, h)
+    ids_g, t_g = m.primary_hits()
+    ids_o, t_o = ob.primary_hits(objs, cam, w, h)
+    assert np.array_equal(ids_g, ids_o) and np.array_equal(bits(t_g), bits(t_o))
+    assert {10, 11, 12, 16, 17, 18}.issubset(set(np.unique(ids_g))) and 13 not in ids_g and 15 not in ids_g
+    assert (t_g[ids_g == 17] < 0).all()  # Q4: the plane accepts a negative t and blocks everything after it
+    assert_render_equal(m, objs, cam, w, h, 8, 77)
+
+
+def test_flags_depth_and_sample_offset():
+    w, h = 120, 80
+    objs, cam = ob.builtin_scene(2), ob.camera_new(w, h)
+    for flags in (_lib.NO_JITTER, _lib.PINHOLE, _lib.NO_JITTER | _lib.PINHOLE):
+        m = forma_b200.create_model(w, h, seed=3, flags=flags)
+        m.scene.load_builtin(2)
+        assert_render_equal(m, objs, cam, w, h, 2, 3, flags=flags)
+    m = forma_b200.create_model(w, h, seed=3)
+    m.scene.load_builtin(2)
+    for depth in (0, 1, 5, 64):
+        assert_render_equal(m, objs, cam, w, h, 2, 3, max_depth=depth)
+    assert_render_equal(m, objs, cam, w, h, 3, 3, sample_offset=1000)
+    with pytest.raises(forma_b200.tracer.FormaError):
+        m.render(1, max_depth=65)
+    with pytest.raises(forma_b200.tracer.FormaError):
+        m.render(0)
+
+
+def test_nan_propagation_matches():
+    """Q10: NaN radiance (zero-length directions) must poison the same pixels on both sides."""
+    objs = np.stack([sphere((0, 0, -1), 0.5, mat=1, col=(float("nan"), 1, 1), fuzz=0.0)])
+    w, h = 48, 48
+    m = forma_b200.create_model(w, h, seed=1)
+    m.scene.load_objects(objs)
+    rgb_g, lin_g = m.render(2, want_linear=True)
+    rgb_o, lin_o, _ = ob.render(objs, ob.camera_new(w, h), w, h, 2, seed=1)
+    assert np.isnan(lin_o).any() and np.array_equal(np.isnan(lin_o), np.isnan(lin_g[..., :3]))
+    assert np.array_equal(rgb_g, rgb_o) and (rgb_g[np.isnan(lin_o)] == 0).all()
+
+
+def test_save_image_png(tmp_path):  # tracer.rs:160-187
+    from PIL import Image
+    w, h = 100, 60
+    m = forma_b200.create_model(w, h, seed=4)
+    p = str(tmp_path / "basic.png")
+    forma_b200.save_image(m, 5, p)
+    rgb_o, _, _ = ob.render(ob.builtin_scene(0), ob.camera_new(w, h), w, h, 5, seed=4)
+    assert np.array_equal(np.asarray(Image.open(p).convert("RGB")), rgb_o)
+    with pytest.raises(forma_b200.tracer.FormaError) as e:
+        forma_b200.save_image(m, 1, str(tmp_path / "no_such_dir" / "basic.png"))
+    assert e.value.code == _lib.EIO
