@@ -1,6 +1,8 @@
 // context.cu — the `forma_rt` handle (TraceModel, tracer.rs:12-17, plus its device mirror) and the
 // C ABI of include/forma_rt.h.  No CPU fallback: every render entry point launches CUDA kernels.
+#include <algorithm>
 #include <cfloat>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -52,7 +54,7 @@ struct DevBuf {
 };
 
 constexpr int kSmemStageLimit = 96 * 1024;   // stage spheres+tris in shared memory up to this size
-constexpr uint32_t kBvhThreshold = 2048;     // ACCEL_AUTO: LBVH at or above this many spheres
+constexpr uint32_t kBvhThreshold = 4;        // ACCEL_AUTO: LBVH at or above this many spheres + triangles
 
 }  // namespace
 
@@ -161,6 +163,90 @@ int upload_scene(forma_rt* c) {
         (kind == FORMA_RT_SPHERE ? ns : kind == FORMA_RT_PLANE ? np : nt)++;
     }
 
+    // ---- acceleration structure planning (host): which primitives the LBVH indexes ----------------
+    // The tree needs every sphere/triangle in ONE run of the list (planes may precede or follow it).
+    int runs = 0;
+    for (const Segment& g : segments) runs += (g.sph_end > g.sph_begin || g.tri_end > g.tri_begin) ? 1 : 0;
+    const bool want_bvh = c->accel == FORMA_RT_ACCEL_LBVH || (c->accel == FORMA_RT_ACCEL_AUTO && ns + nt >= kBvhThreshold);
+    if (c->accel == FORMA_RT_ACCEL_LBVH && runs > 1)
+        return fail(FORMA_RT_EINVAL, "LBVH needs all spheres and triangles in one plane-free run of Scene.objects; use FORMA_RT_ACCEL_BRUTE");
+    LbvhInput bin{};
+    bool use_bvh = false;
+    float bc[3] = {0, 0, 0}, br2 = 0.0f, beps = 0.0f;
+    if (want_bvh && runs == 1 && ns + nt >= 2) {
+        const int NS = (int)ns, NT = (int)nt, N = NS + NT;
+        std::vector<V3> lo(N), hi(N);
+        for (int i = 0; i < NS; ++i) {
+            const float4 sp = spheres[i];
+            lo[i] = {sp.x - sp.w, sp.y - sp.w, sp.z - sp.w};
+            hi[i] = {sp.x + sp.w, sp.y + sp.w, sp.z + sp.w};
+        }
+        for (int t = 0; t < NT; ++t) {
+            const float4 a = tris[3 * t], e1 = tris[3 * t + 1], e2 = tris[3 * t + 2];
+            const float x[3] = {a.x, a.x + e1.x, a.x + e2.x}, y[3] = {a.y, a.y + e1.y, a.y + e2.y}, z[3] = {a.z, a.z + e1.z, a.z + e2.z};
+            lo[NS + t] = {std::min({x[0], x[1], x[2]}), std::min({y[0], y[1], y[2]}), std::min({z[0], z[1], z[2]})};
+            hi[NS + t] = {std::max({x[0], x[1], x[2]}), std::max({y[0], y[1], y[2]}), std::max({z[0], z[1], z[2]})};
+        }
+        auto extent = [&](int i) { return std::max({hi[i].x - lo[i].x, hi[i].y - lo[i].y, hi[i].z - lo[i].z}); };
+        // "big" primitives (a ground sphere of radius 1000 among unit spheres, a floor quad) would wreck the
+        // Morton grid and the upper tree levels: they are scanned linearly instead.  Only for large scenes.
+        std::vector<char> big(N, 0);
+        if (N >= 64) {
+            for (int pass = 0; pass < 3; ++pass) {
+                V3 ulo{FLT_MAX, FLT_MAX, FLT_MAX}, uhi{-FLT_MAX, -FLT_MAX, -FLT_MAX};
+                for (int i = 0; i < N; ++i) if (!big[i] && std::isfinite(extent(i))) {
+                    ulo = {std::min(ulo.x, lo[i].x), std::min(ulo.y, lo[i].y), std::min(ulo.z, lo[i].z)};
+                    uhi = {std::max(uhi.x, hi[i].x), std::max(uhi.y, hi[i].y), std::max(uhi.z, hi[i].z)};
+                }
+                const float E = std::max({uhi.x - ulo.x, uhi.y - ulo.y, uhi.z - ulo.z});
+                bool changed = false;
+                for (int i = 0; i < N; ++i) if (!big[i] && !(extent(i) <= 0.25f * E)) { big[i] = 1; changed = true; }
+                if (!changed) break;
+            }
+            int nbig = 0;
+            for (int i = 0; i < N; ++i) nbig += big[i];
+            if (nbig > 256 || N - nbig < 2) std::fill(big.begin(), big.end(), 0);
+        }
+        for (int i = 0; i < N; ++i) if (!std::isfinite(extent(i))) big[i] = 1;  // NaN/inf geometry stays on the exact scan
+        // stable partition of the packed arrays: big first
+        auto partition = [&](int first, int count, int stride, std::vector<float4>& data, std::vector<int>& objs_idx) {
+            std::vector<float4> d2; std::vector<int> o2; d2.reserve(data.size()); o2.reserve(objs_idx.size());
+            int nb = 0;
+            for (int pass = 1; pass >= 0; --pass)
+                for (int i = 0; i < count; ++i) if (big[first + i] == pass) {
+                    for (int k = 0; k < stride; ++k) d2.push_back(data[stride * i + k]);
+                    o2.push_back(objs_idx[i]);
+                    nb += pass;
+                }
+            data.swap(d2); objs_idx.swap(o2);
+            return nb;
+        };
+        std::vector<V3> blo, bhi;  // boxes of what goes into the tree, for the Morton grid / bounding sphere
+        for (int i = 0; i < N; ++i) if (!big[i]) { blo.push_back(lo[i]); bhi.push_back(hi[i]); }
+        if ((int)blo.size() >= 2) {
+            const int big_s = partition(0, NS, 1, spheres, sphere_obj);
+            const int big_t = partition(NS, NT, 3, tris, tri_obj);
+            V3 clo{FLT_MAX, FLT_MAX, FLT_MAX}, chi{-FLT_MAX, -FLT_MAX, -FLT_MAX}, ulo = clo, uhi = chi;
+            for (size_t i = 0; i < blo.size(); ++i) {
+                const V3 cc{0.5f * (blo[i].x + bhi[i].x), 0.5f * (blo[i].y + bhi[i].y), 0.5f * (blo[i].z + bhi[i].z)};
+                clo = {std::min(clo.x, cc.x), std::min(clo.y, cc.y), std::min(clo.z, cc.z)};
+                chi = {std::max(chi.x, cc.x), std::max(chi.y, cc.y), std::max(chi.z, cc.z)};
+                ulo = {std::min(ulo.x, blo[i].x), std::min(ulo.y, blo[i].y), std::min(ulo.z, blo[i].z)};
+                uhi = {std::max(uhi.x, bhi[i].x), std::max(uhi.y, bhi[i].y), std::max(uhi.z, bhi[i].z)};
+            }
+            bin.n_spheres = NS; bin.n_tris = NT; bin.big_spheres = big_s; bin.big_tris = big_t;
+            bin.n_bvh_spheres = NS - big_s; bin.count = (NS - big_s) + (NT - big_t);
+            const float cl[3] = {clo.x, clo.y, clo.z}, ch[3] = {chi.x, chi.y, chi.z};
+            for (int k = 0; k < 3; ++k) { bin.cmin[k] = cl[k]; bin.cscale[k] = ch[k] > cl[k] ? 1024.0f / (ch[k] - cl[k]) : 0.0f; }
+            bc[0] = 0.5f * (ulo.x + uhi.x); bc[1] = 0.5f * (ulo.y + uhi.y); bc[2] = 0.5f * (ulo.z + uhi.z);
+            const V3 half{0.5f * (uhi.x - ulo.x), 0.5f * (uhi.y - ulo.y), 0.5f * (uhi.z - ulo.z)};
+            br2 = 1.0001f * dot(half, half);
+            const float scale = std::max({std::fabs(ulo.x), std::fabs(ulo.y), std::fabs(ulo.z), std::fabs(uhi.x), std::fabs(uhi.y), std::fabs(uhi.z)});
+            beps = std::ldexp(scale, -16) + 1e-30f;
+            use_bvh = true;
+        }
+    }
+
     cudaStream_t s = c->stream;
     CU_TRY(c->d_spheres.upload(spheres, s));
     CU_TRY(c->d_tris.upload(tris, s));
@@ -184,24 +270,21 @@ int upload_scene(forma_rt* c) {
     v.n_spheres = (int)ns; v.n_tris = (int)nt; v.n_planes = (int)np;
     v.bvh_nodes = nullptr;
 
-    // acceleration structure: LBVH over the spheres when asked for / when the scan would be long.
-    // The tree needs every sphere in one segment (planes, if any, first in the list or absent).
-    bool want_bvh = c->accel == FORMA_RT_ACCEL_LBVH || (c->accel == FORMA_RT_ACCEL_AUTO && ns >= kBvhThreshold);
-    bool one_run = true;
-    for (const Segment& g : segments)
-        if (g.sph_end > g.sph_begin && !(g.sph_begin == 0 && g.sph_end == (int)ns)) one_run = false;
+    v.bvh_prim = nullptr; v.big_spheres = 0; v.big_tris = 0;
     c->stats.bvh_nodes = 0;
     c->stats.accel_in_use = FORMA_RT_ACCEL_BRUTE;
-    if (want_bvh && ns >= 2) {
-        if (!one_run)
-            return fail(FORMA_RT_EINVAL, "LBVH needs all spheres in one plane-free run of Scene.objects; use FORMA_RT_ACCEL_BRUTE");
-        cudaError_t e = c->bvh.build(c->d_spheres.p, (int)ns, s);
+    if (use_bvh) {
+        bin.spheres = c->d_spheres.p; bin.tris = c->d_tris.p;
+        cudaError_t e = c->bvh.build(bin, s);
         if (e != cudaSuccess) return fail(FORMA_RT_ECUDA, std::string("LBVH build: ") + cudaGetErrorString(e));
-        v.bvh_nodes = c->bvh.nodes;
-        c->stats.bvh_nodes = (uint32_t)(ns - 1);
+        v.bvh_nodes = c->bvh.nodes; v.bvh_prim = c->bvh.prim;
+        v.big_spheres = bin.big_spheres; v.big_tris = bin.big_tris;
+        v.bvh_center[0] = bc[0]; v.bvh_center[1] = bc[1]; v.bvh_center[2] = bc[2];
+        v.bvh_r2 = br2; v.bvh_eps = beps;
+        c->stats.bvh_nodes = (uint32_t)(bin.count - 1);
         c->stats.accel_in_use = FORMA_RT_ACCEL_LBVH;
     }
-    const size_t stage = (v.bvh_nodes ? 0 : spheres.size() * sizeof(float4)) + tris.size() * sizeof(float4);
+    const size_t stage = spheres.size() * sizeof(float4) + tris.size() * sizeof(float4);
     v.smem_bytes = (!v.bvh_nodes && stage > 0 && stage <= (size_t)kSmemStageLimit) ? (int)stage : 0;
 
     c->stats.n_objects = (uint32_t)n;

@@ -45,6 +45,11 @@ struct SceneView {
     const int* ids;
     // LBVH over spheres[0 .. n_spheres) (nullptr = brute force)
     const float4* bvh_nodes;   // 4 float4 per internal node: see lbvh.cu
+    const int* bvh_prim;       // unified primitive index (< n_spheres: sphere) of sorted leaf l
+    int big_spheres, big_tris; // with a tree: the first big_* packed primitives are scanned linearly
+    float bvh_center[3];       // bounding sphere of everything the tree indexes
+    float bvh_r2;              // its radius squared
+    float bvh_eps;             // absolute box pad: 2^-16 x scene scale
     int n_segments;
     int n_spheres;
     int n_tris;

@@ -134,6 +134,128 @@ struct HitState {
 
 constexpr float kTMin = 0.001f;  // tracer.rs:191
 
+// Winner of the segment being scanned.  The reference scans in list order with strict `<`
+// (tracer.rs:196, sphere.rs:32), i.e. it keeps the lexicographic minimum of (t, list index).  Taking
+// a candidate iff `t < closest || (t == closest && its list index < the winner's)` gives the same
+// result in ANY visiting order, which is what lets spheres, triangles and the LBVH walk be scanned
+// separately.  A winner of an earlier segment always has a smaller list index, so ties never beat it.
+struct Winner {
+    int kind = -1;  // -1 none in this segment, 0 sphere, 2 triangle
+    int slot = 0;   // packed index
+    int obj = 0;    // list index
+};
+
+// Sphere::hit (sphere.rs:23-51).  The candidate root does not depend on t_max: root_one if it
+// exceeds t_min, else root_two; if root_one >= t_max then root_two >= root_one fails too.
+__device__ __forceinline__ void try_sphere(const SceneView& S, const float4* __restrict__ sph, int i, float3 o,
+                                           float3 d, float a, HitState& h, Winner& w) {
+    const float4 s = sph[i];
+    const float3 oc = o - xyz(s);
+    const float b = dot(oc, d);
+    const float c = dot(oc, oc) - s.w * s.w;
+    const float disc = b * b - a * c;
+    if (disc > 0.0f) {
+        const float sq = sqrtf(disc);
+        float root = (-b - sq) / a;
+        if (!(root > kTMin)) root = (-b + sq) / a;
+        if (root > kTMin && root <= h.closest) {
+            bool take = root < h.closest;
+            int obj = -1;
+            if (!take && w.kind >= 0) { obj = S.sphere_obj[i]; take = obj < w.obj; }
+            if (take) { h.closest = root; w.kind = 0; w.slot = i; w.obj = obj >= 0 ? obj : S.sphere_obj[i]; }
+        }
+    }
+}
+
+// Triangle extension (DESIGN.md "Scene mapping"): division-free inside test, one division for t.
+__device__ __forceinline__ void try_triangle(const SceneView& S, const float4* __restrict__ tri, int i, float3 o,
+                                             float3 d, HitState& h, Winner& w) {
+    const float4 q0 = tri[3 * i], q1 = tri[3 * i + 1], q2 = tri[3 * i + 2];
+    const float3 e1 = xyz(q1), e2 = xyz(q2);
+    const float3 pvec = cross(d, e2);
+    const float det = dot(e1, pvec);
+    const float3 tvec = o - xyz(q0);
+    const float uu = dot(tvec, pvec);
+    const bool pos = det > 0.0f;
+    // first half of the inside test before paying for qvec
+    if (det != 0.0f && (pos ? uu >= 0.0f : uu <= 0.0f)) {
+        const float3 qvec = cross(tvec, e1);
+        const float vv = dot(d, qvec);
+        const bool inside = pos ? (vv >= 0.0f && uu + vv <= det) : (vv <= 0.0f && uu + vv >= det);
+        if (inside) {
+            const float t = dot(e2, qvec) / det;
+            if (t > kTMin && t <= h.closest) {
+                bool take = t < h.closest;
+                int obj = -1;
+                if (!take && w.kind >= 0) { obj = S.tri_obj[i]; take = obj < w.obj; }
+                if (take) { h.closest = t; w.kind = 2; w.slot = i; w.obj = obj >= 0 ? obj : S.tri_obj[i]; }
+            }
+        }
+    }
+}
+
+// LBVH walk over the primitives the tree indexes (lbvh.cu).  Exactness: a child box is visited iff
+// the ray's interval through the PADDED box reaches [0, closest]; the pad
+//     coef(ray) * q(child) + eps,   coef = 2^-19 (|o - C|^2 + R^2),  q = max 1/r below the child
+// exceeds the largest miss distance at which the f32 test of sphere.rs:25-29 can still report
+// disc > 0 (|disc error| <= 25 eps_f32 a L^2, L <= |o - C| + R), and eps = 2^-16 x scene scale covers
+// the triangle test's and the slab test's own rounding.  So no primitive the scan would accept is
+// culled, and the tie rule makes the visiting order irrelevant.
+__device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __restrict__ sph,
+                                            const float4* __restrict__ tri, float3 o, float3 d, float a,
+                                            HitState& h, Winner& w) {
+    const float huge = 1e30f;
+    const float ix = fabsf(d.x) < 1e-30f ? copysignf(huge, d.x) : 1.0f / d.x;
+    const float iy = fabsf(d.y) < 1e-30f ? copysignf(huge, d.y) : 1.0f / d.y;
+    const float iz = fabsf(d.z) < 1e-30f ? copysignf(huge, d.z) : 1.0f / d.z;
+    const float ox = -o.x * ix, oy = -o.y * iy, oz = -o.z * iz;
+    const float3 oc = o - f3(S.bvh_center);
+    const float coef = 1.9073486e-6f * (dot(oc, oc) + S.bvh_r2);  // 2^-19
+    const float eps = S.bvh_eps;
+
+    int stack[64];
+    int sp = 0;
+    int node = 0;
+    for (;;) {
+        const float4 n0 = __ldg(S.bvh_nodes + 4 * node), n1 = __ldg(S.bvh_nodes + 4 * node + 1);
+        const float4 n2 = __ldg(S.bvh_nodes + 4 * node + 2), n3 = __ldg(S.bvh_nodes + 4 * node + 3);
+        const float padL = __fmaf_rn(coef, n3.z, eps), padR = __fmaf_rn(coef, n3.w, eps);
+        // slab test, (b - o) / d as fma(b, 1/d, -o/d); explicit fma: this part need not match the oracle
+        float t0 = __fmaf_rn(n0.x - padL, ix, ox), t1 = __fmaf_rn(n0.w + padL, ix, ox);
+        float nearL = fminf(t0, t1), farL = fmaxf(t0, t1);
+        t0 = __fmaf_rn(n0.y - padL, iy, oy); t1 = __fmaf_rn(n1.x + padL, iy, oy);
+        nearL = fmaxf(nearL, fminf(t0, t1)); farL = fminf(farL, fmaxf(t0, t1));
+        t0 = __fmaf_rn(n0.z - padL, iz, oz); t1 = __fmaf_rn(n1.y + padL, iz, oz);
+        nearL = fmaxf(fmaxf(nearL, fminf(t0, t1)), 0.0f); farL = fminf(fminf(farL, fmaxf(t0, t1)), h.closest);
+        t0 = __fmaf_rn(n1.z - padR, ix, ox); t1 = __fmaf_rn(n2.y + padR, ix, ox);
+        float nearR = fminf(t0, t1), farR = fmaxf(t0, t1);
+        t0 = __fmaf_rn(n1.w - padR, iy, oy); t1 = __fmaf_rn(n2.z + padR, iy, oy);
+        nearR = fmaxf(nearR, fminf(t0, t1)); farR = fminf(farR, fmaxf(t0, t1));
+        t0 = __fmaf_rn(n2.x - padR, iz, oz); t1 = __fmaf_rn(n2.w + padR, iz, oz);
+        nearR = fmaxf(fmaxf(nearR, fminf(t0, t1)), 0.0f); farR = fminf(fminf(farR, fmaxf(t0, t1)), h.closest);
+        const bool hitL = nearL <= farL, hitR = nearR <= farR;
+        int cL = __float_as_int(n3.x), cR = __float_as_int(n3.y);
+        int next = -1;   // internal node to descend into
+        bool have = false;
+        if (hitL && hitR) {
+            if (nearR < nearL) { const int t = cL; cL = cR; cR = t; }  // cL = nearer child
+            // leaves are tested on the spot, internal nodes are descended / pushed
+            if (cL < 0) { const int p = S.bvh_prim[~cL]; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
+            else { next = cL; have = true; }
+            if (cR < 0) { const int p = S.bvh_prim[~cR]; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
+            else if (have) { stack[sp++] = cR; }
+            else { next = cR; have = true; }
+        } else if (hitL || hitR) {
+            const int c = hitL ? cL : cR;
+            if (c < 0) { const int p = S.bvh_prim[~c]; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
+            else { next = c; have = true; }
+        }
+        if (have) { node = next; continue; }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+}
+
 template <bool SMEM>
 __device__ __forceinline__ void closest_hit(const SceneView& S, const float4* __restrict__ sph,
                                             const float4* __restrict__ tri, float3 o, float3 d, HitState& h) {
@@ -142,60 +264,26 @@ __device__ __forceinline__ void closest_hit(const SceneView& S, const float4* __
     const float a = dot(d, d);  // sphere.rs:25
     for (int sg = 0; sg < S.n_segments; ++sg) {
         const Segment g = S.segments[sg];
-        int win_kind = -1, win_slot = 0;
-        // spheres of the segment, list order (sphere.rs:23-51)
-        for (int i = g.sph_begin; i < g.sph_end; ++i) {
-            const float4 s = sph[i];
-            float3 oc = o - xyz(s);
-            float b = dot(oc, d);
-            float c = dot(oc, oc) - s.w * s.w;
-            float disc = b * b - a * c;
-            if (disc > 0.0f) {
-                float sq = sqrtf(disc);
-                float root = (-b - sq) / a;
-                if (root > kTMin && root < h.closest) {
-                    h.closest = root; win_kind = 0; win_slot = i;
-                } else {
-                    root = (-b + sq) / a;
-                    if (root > kTMin && root < h.closest) { h.closest = root; win_kind = 0; win_slot = i; }
-                }
-            }
-        }
-        // triangles of the segment (extension; DESIGN.md "Triangle extension")
-        for (int i = g.tri_begin; i < g.tri_end; ++i) {
-            const float4 q0 = tri[3 * i], q1 = tri[3 * i + 1], q2 = tri[3 * i + 2];
-            float3 e1 = xyz(q1), e2 = xyz(q2);
-            float3 pvec = cross(d, e2);
-            float det = dot(e1, pvec);
-            float3 tvec = o - xyz(q0);
-            float uu = dot(tvec, pvec);
-            bool pos = det > 0.0f;
-            // first half of the inside test before paying for qvec
-            if (!(det != 0.0f) || !(pos ? uu >= 0.0f : uu <= 0.0f)) continue;
-            float3 qvec = cross(tvec, e1);
-            float vv = dot(d, qvec);
-            bool inside = pos ? (vv >= 0.0f && uu + vv <= det) : (vv <= 0.0f && uu + vv >= det);
-            if (!inside) continue;
-            float t = dot(e2, qvec) / det;
-            if (t > kTMin) {
-                bool take = t < h.closest;
-                if (!take && t == h.closest && win_kind == 0) take = S.tri_obj[i] < S.sphere_obj[win_slot];
-                if (take) { h.closest = t; win_kind = 2; win_slot = i; }
-            }
-        }
-        if (win_kind >= 0) {  // what the last accepting hit() left in the shared HitRecord
+        Winner w;
+        // With an LBVH the tree holds all but the first big_* primitives of the (single) run
+        const bool tree = S.bvh_nodes != nullptr && g.sph_end + g.tri_end > g.sph_begin + g.tri_begin;
+        const int sph_end = tree ? S.big_spheres : g.sph_end;
+        const int tri_end = tree ? S.big_tris : g.tri_end;
+        for (int i = g.sph_begin; i < sph_end; ++i) try_sphere(S, sph, i, o, d, a, h, w);
+        for (int i = g.tri_begin; i < tri_end; ++i) try_triangle(S, tri, i, o, d, h, w);
+        if (tree) bvh_closest(S, sph, tri, o, d, a, h, w);
+        if (w.kind >= 0) {  // what the last accepting hit() left in the shared HitRecord
             h.t = h.closest;
             h.p = o + h.t * d;  // ray.rs:30-32
-            if (win_kind == 0) {
-                const float4 s = sph[win_slot];
+            if (w.kind == 0) {
+                const float4 s = sph[w.slot];
                 h.n = (h.p - xyz(s)) / s.w;  // sphere.rs:35,44
-                h.obj = S.sphere_obj[win_slot];
             } else {
-                float3 n = f3(tri[3 * win_slot].w, tri[3 * win_slot + 1].w, tri[3 * win_slot + 2].w);
+                float3 n = f3(tri[3 * w.slot].w, tri[3 * w.slot + 1].w, tri[3 * w.slot + 2].w);
                 if (dot(d, n) > 0.0f) n = n * -1.0f;
                 h.n = n;
-                h.obj = S.tri_obj[win_slot];
             }
+            h.obj = w.obj;
         }
         if (g.plane >= 0) {  // plane.rs:24-44 (Q4: range test on denom; Q5: t, p written before the extent test)
             const float3 position = xyz(S.planes[3 * g.plane]);

@@ -1,0 +1,109 @@
+"""-m gpu: the LBVH walk must return exactly what the linear scan returns (same ids, same t bits,
+same images), on the oracle at sizes it can finish and against the GPU's own brute-force scan at
+BASELINE config D's size (100 000 spheres + ground)."""
+import importlib.util
+import json
+import os
+
+import numpy as np
+import pytest
+
+import forma_b200
+from forma_b200 import _lib
+from oracle import binding as ob
+from oracle import scene_oracle as so
+
+from conftest import ROOT, load_scene_pair
+
+pytestmark = pytest.mark.gpu
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def generator():
+    spec = importlib.util.spec_from_file_location("sphere_scene_generator",
+                                                  os.path.join(ROOT, "python-extras", "sphere_scene_generator.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def model(txt, w, h, accel, seed=0):
+    m = forma_b200.create_model(w, h, seed=seed, accel=accel)
+    m.scene.load_json(txt)
+    m.scene.camera.use_json()
+    return m
+
+
+@pytest.mark.parametrize("name", ["scene_01", "scene_05", "scene_06", "scene_09"])
+def test_lbvh_equals_scan_on_reference_scenes(name):
+    w, h = 480, 270
+    txt, objs, cam = load_scene_pair(name, w, h)
+    mb, ms = model(txt, w, h, _lib.ACCEL_LBVH, 8), model(txt, w, h, _lib.ACCEL_BRUTE, 8)
+    ids_b, t_b = mb.primary_hits()
+    ids_s, t_s = ms.primary_hits()
+    assert mb.stats().accel_in_use == _lib.ACCEL_LBVH and ms.stats().accel_in_use == _lib.ACCEL_BRUTE
+    assert mb.stats().bvh_nodes > 0
+    assert np.array_equal(ids_b, ids_s) and np.array_equal(bits(t_b), bits(t_s))
+    ids_o, t_o = ob.primary_hits(objs, cam, w, h)
+    assert np.array_equal(ids_b, ids_o) and np.array_equal(bits(t_b), bits(t_o))
+    rb, lb = mb.render(2, want_linear=True)
+    rs, ls = ms.render(2, want_linear=True)
+    assert mb.stats().rays == ms.stats().rays
+    assert np.array_equal(bits(lb), bits(ls)) and np.array_equal(rb, rs)
+
+
+def test_lbvh_sphere_field_vs_oracle():
+    """2 000 spheres + the radius-1000 ground (a "big" primitive kept out of the tree): oracle parity."""
+    d = generator().generate(2000, seed=99)
+    txt = json.dumps(d)
+    w, h = 256, 144
+    objs = so.flatten(d)
+    fr, at, up, fov = so.json_camera(d)
+    cam = ob.camera_look(fr, at, up, fov, w / h)
+    m = model(txt, w, h, _lib.ACCEL_AUTO, 21)
+    st0 = m.stats()
+    ids, t = m.primary_hits()
+    assert m.stats().accel_in_use == _lib.ACCEL_LBVH and m.stats().bvh_nodes == 2000 - 1
+    ids_o, t_o = ob.primary_hits(objs, cam, w, h)
+    assert np.array_equal(ids, ids_o) and np.array_equal(bits(t), bits(t_o))
+    rgb, lin = m.render(2, want_linear=True)
+    rgb_o, lin_o, rays_o = ob.render(objs, cam, w, h, 2, seed=21, nthreads=os.cpu_count())
+    assert m.stats().rays == rays_o
+    assert np.array_equal(bits(lin[..., :3]), bits(lin_o)) and np.array_equal(rgb, rgb_o)
+
+
+def test_config_d_100k_lbvh_equals_gpu_scan():
+    """BASELINE config D at full scene size: 100 000 spheres + ground, 1920x1080 primary rays, and a
+    1-spp depth-50 frame at 960x540 — LBVH vs the GPU's own linear scan, bit for bit."""
+    txt = json.dumps(generator().generate(100_000, seed=1234))
+    w, h = 1920, 1080
+    mb, ms = model(txt, w, h, _lib.ACCEL_LBVH, 5), model(txt, w, h, _lib.ACCEL_BRUTE, 5)
+    ids_b, t_b = mb.primary_hits()
+    ids_s, t_s = ms.primary_hits()
+    assert mb.stats().bvh_nodes == 100_000 - 1
+    assert np.array_equal(ids_b, ids_s) and np.array_equal(bits(t_b), bits(t_s))
+    assert (ids_b >= 0).mean() > 0.5 and len(np.unique(ids_b)) > 5000
+    w, h = 480, 270
+    mb, ms = model(txt, w, h, _lib.ACCEL_LBVH, 5), model(txt, w, h, _lib.ACCEL_BRUTE, 5)
+    rb, lb = mb.render(1, want_linear=True)
+    rs, ls = ms.render(1, want_linear=True)
+    assert mb.stats().rays == ms.stats().rays > w * h * 2
+    assert np.array_equal(bits(lb), bits(ls)) and np.array_equal(rb, rs)
+
+
+def test_lbvh_rejects_interleaved_planes():
+    from test_oracle_analytic import plane, sphere
+    objs = np.stack([sphere((0, 0, -3), 1.0), plane((0, 0, -9), (0, 0, -1), (5, 5, 5)), sphere((1, 0, -3), 1.0),
+                     sphere((2, 0, -3), 1.0), sphere((3, 0, -3), 1.0), sphere((4, 0, -3), 1.0)])
+    m = forma_b200.create_model(32, 32, accel=_lib.ACCEL_LBVH)
+    m.scene.load_objects(objs)
+    with pytest.raises(forma_b200.tracer.FormaError):
+        m.primary_hits()
+    m2 = forma_b200.create_model(32, 32, accel=_lib.ACCEL_AUTO)  # AUTO falls back to the scan
+    m2.scene.load_objects(objs)
+    ids, _ = m2.primary_hits()
+    assert m2.stats().accel_in_use == _lib.ACCEL_BRUTE
+    assert np.array_equal(ids, ob.primary_hits(objs, ob.camera_new(32, 32), 32, 32)[0])
