@@ -140,33 +140,6 @@ def run_reference(args):
         "gpu_launches": 0}), flush=True)
 
 
-def setup_exchange(m, dist, rank, world, dev):
-    """Sample-split exchange plumbing: every rank exports its f32 sum buffer (and rank 0 its RGB8
-    frame) through CUDA IPC; handles travel by torch.distributed.  Returns a dict or None (-> NCCL)."""
-    import torch
-    npix = W * H
-    try:
-        from forma_b200 import _lib
-        import ctypes
-        p = ctypes.c_void_p()
-        _lib.check(_lib.lib().forma_rt_device_alloc(m._h, npix * 16, ctypes.byref(p)))
-        q = ctypes.c_void_p()
-        _lib.check(_lib.lib().forma_rt_device_alloc(m._h, npix * 3, ctypes.byref(q)))
-        mine = torch.tensor(list(m.ipc_export(p.value) + m.ipc_export(q.value)), dtype=torch.uint8, device=dev)
-        allh = [torch.empty_like(mine) for _ in range(world)]
-        dist.all_gather(allh, mine)
-        sums, rgb0 = [], None
-        for r, t in enumerate(allh):
-            b = bytes(t.cpu().numpy().tobytes())
-            sums.append(p.value if r == rank else m.ipc_open(b[:64]))
-            if r == 0:
-                rgb0 = q.value if rank == 0 else m.ipc_open(b[64:])
-        return {"sum": p.value, "peer_sums": sums, "rgb0": rgb0, "mode": "fused peer-memory reduce+tonemap (CUDA IPC over NVLink)"}
-    except Exception as e:  # noqa: BLE001 — fall back to NCCL reduce, and say so in the JSON line
-        sys.stderr.write(f"[bench] rank {rank}: IPC exchange unavailable ({e}); using NCCL reduce\n")
-        return None
-
-
 def run_ours(args):
     import torch
     import forma_b200
@@ -195,13 +168,17 @@ def run_ours(args):
     ex = None
     d_sum = None
     if world > 1:
-        ex = setup_exchange(m, dist, rank, world, dev)
+        try:
+            from forma_b200.distributed import FusedExchange
+            ex = FusedExchange(m, dist, dev)
+        except Exception as e:  # noqa: BLE001 — fall back to NCCL reduce, and say so in the JSON line
+            sys.stderr.write(f"[bench] rank {rank}: IPC exchange unavailable ({e}); using NCCL reduce\n")
+            ex = None
         ok = torch.tensor([1 if ex else 0], device=dev)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if not ok.item():
             ex = None
             d_sum = torch.empty((npix, 4), dtype=torch.float32, device=dev)
-    lo, hi = npix * rank // world, npix * (rank + 1) // world
 
     def step():
         """One frame on this rank; returns kernels launched."""
@@ -209,11 +186,7 @@ def run_ours(args):
             m.render_device(SPP, 0, DEPTH, d_rgb.data_ptr(), None, stream)
             return 1
         if ex:
-            m.render_device(SPP, rank * SPP, DEPTH, None, ex["sum"], stream)
-            dist.barrier()  # every rank's partial sums are complete in its HBM
-            m.reduce_tonemap_device(ex["peer_sums"], SPP * world, lo, hi, ex["rgb0"], None, stream)
-            dist.barrier()  # rank 0's frame is complete
-            return 2
+            return ex.frame(SPP, DEPTH, stream)
         m.render_device(SPP, rank * SPP, DEPTH, None, d_sum.data_ptr(), stream)
         dist.reduce(d_sum, dst=0)
         if rank == 0:
@@ -268,7 +241,7 @@ def run_ours(args):
             else:
                 step()
                 if rank == 0:
-                    src = ex["rgb0"] if ex else d_rgb.data_ptr()
+                    src = ex.rgb0 if ex else d_rgb.data_ptr()
                     _d2h(hp, src, npix * 3)
         for _ in range(2):
             e2e_step()
@@ -290,7 +263,7 @@ def run_ours(args):
 
     if rank == 0:
         emit(args, world, value, ms_per_step, rays_step, kern_ms, st, clk.summary(), e2e, launches, t_wall,
-             ex["mode"] if ex else ("NCCL reduce + tonemap" if world > 1 else None))
+             ex.mode if ex else ("NCCL reduce + tonemap" if world > 1 else None))
     if dist:
         dist.barrier()
         dist.destroy_process_group()
