@@ -54,7 +54,7 @@ struct DevBuf {
 };
 
 constexpr int kSmemStageLimit = 96 * 1024;   // stage spheres+tris in shared memory up to this size
-constexpr uint32_t kBvhThreshold = 4;        // ACCEL_AUTO: LBVH at or above this many spheres + triangles
+constexpr uint32_t kBvhThreshold = 16;       // ACCEL_AUTO: LBVH at or above this many spheres + triangles
 
 }  // namespace
 
@@ -270,6 +270,26 @@ int upload_scene(forma_rt* c) {
     v.n_spheres = (int)ns; v.n_tris = (int)nt; v.n_planes = (int)np;
     v.bvh_nodes = nullptr;
 
+    {   // closest_hit's conservative cull: bounding sphere of the box around every sphere and triangle
+        V3 ulo{FLT_MAX, FLT_MAX, FLT_MAX}, uhi{-FLT_MAX, -FLT_MAX, -FLT_MAX};
+        bool finite = true;
+        auto grow = [&](float x, float y, float z, float r) {
+            finite = finite && std::isfinite(x) && std::isfinite(y) && std::isfinite(z) && std::isfinite(r);
+            r = std::fabs(r);
+            ulo = {std::min(ulo.x, x - r), std::min(ulo.y, y - r), std::min(ulo.z, z - r)};
+            uhi = {std::max(uhi.x, x + r), std::max(uhi.y, y + r), std::max(uhi.z, z + r)};
+        };
+        for (const float4& sp : spheres) grow(sp.x, sp.y, sp.z, sp.w);
+        for (size_t t = 0; t + 2 < tris.size(); t += 3) {
+            const float4 a = tris[t], e1 = tris[t + 1], e2 = tris[t + 2];
+            grow(a.x, a.y, a.z, 0.0f); grow(a.x + e1.x, a.y + e1.y, a.z + e1.z, 0.0f); grow(a.x + e2.x, a.y + e2.y, a.z + e2.z, 0.0f);
+        }
+        const V3 half{0.5f * (uhi.x - ulo.x), 0.5f * (uhi.y - ulo.y), 0.5f * (uhi.z - ulo.z)};
+        const float r2 = 1.0001f * dot(half, half);
+        v.cull_center[0] = 0.5f * (ulo.x + uhi.x); v.cull_center[1] = 0.5f * (ulo.y + uhi.y); v.cull_center[2] = 0.5f * (ulo.z + uhi.z);
+        v.cull_r2 = (finite && ns + nt > 0 && std::isfinite(r2)) ? r2 : INFINITY;
+        if (!(v.cull_r2 < INFINITY)) v.cull_center[0] = v.cull_center[1] = v.cull_center[2] = 0.0f;
+    }
     v.bvh_prim = nullptr; v.big_spheres = 0; v.big_tris = 0;
     c->stats.bvh_nodes = 0;
     c->stats.accel_in_use = FORMA_RT_ACCEL_BRUTE;

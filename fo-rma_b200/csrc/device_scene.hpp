@@ -50,6 +50,8 @@ struct SceneView {
     float bvh_center[3];       // bounding sphere of everything the tree indexes
     float bvh_r2;              // its radius squared
     float bvh_eps;             // absolute box pad: 2^-16 x scene scale
+    float cull_center[3];      // bounding sphere of every finite sphere and triangle (closest_hit's cull);
+    float cull_r2;             // radius squared; +inf = never cull
     int n_segments;
     int n_spheres;
     int n_tris;

@@ -50,15 +50,51 @@ __global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ 
         const float fx = (float)x, fy = (float)(P.height - y);  // tracer.rs:171-172 (Q1: height - y)
         const float fw = (float)P.width, fh = (float)P.height;
         const bool no_jitter = P.flags & FORMA_RT_NO_JITTER, pinhole = P.flags & FORMA_RT_PINHOLE;
-        for (uint32_t s = 0; s < P.spp; ++s) {
-            rng.sample = P.sample_offset + s;
-            Rand4 r0 = rng.block(0, 0);
-            if (no_jitter) { r0.x = 0.5f; r0.y = 0.5f; }
-            const float u = (fx + r0.x) / fw;
-            const float v = (fy + r0.y) / fh;
-            float3 o, d;
-            camera_ray(P.cam, rng, r0, u, v, pinhole, o, d);
-            col = col + get_color<SMEM>(P.scene, sph, tri, rng, o, d, P.max_depth, rays);  // tracer.rs:174
+        // tracer.rs:168-175's sample loop and get_color's recursion (tracer.rs:189-219) as ONE flat
+        // loop of closest-hit queries: a lane whose path ended starts the next sample of its own pixel
+        // in the same iteration the other lanes spend on their next bounce, so a warp runs for the
+        // longest per-pixel SUM of path lengths, not for spp x the longest path.  Per pixel the samples
+        // are still traced and added in order, so the f32 sums match the reference's loop exactly.
+        int stack[kMaxDepthCap];  // list indices of the hit objects: attenuations multiply innermost first
+        uint32_t s = 0, depth = 0;
+        bool alive = false;
+        float3 o = f3(0.0f, 0.0f, 0.0f), d = o;
+        for (;;) {
+            if (!alive) {
+                if (s >= P.spp) break;
+                rng.sample = P.sample_offset + s;
+                Rand4 r0 = rng.block(0, 0);
+                if (no_jitter) { r0.x = 0.5f; r0.y = 0.5f; }
+                const float u = (fx + r0.x) / fw;
+                const float v = (fy + r0.y) / fh;
+                camera_ray(P.cam, rng, r0, u, v, pinhole, o, d);
+                depth = 0;
+                alive = true;
+            }
+            HitState h;
+            ++rays;
+            closest_hit<SMEM>(P.scene, sph, tri, o, d, h);
+            float3 pc = f3(0.0f, 0.0f, 0.0f);
+            bool done = true;
+            if (h.obj < 0) pc = sky(d);                      // tracer.rs:213-217
+            else if (depth < P.max_depth) {                  // tracer.rs:205
+                float3 no, nd;
+                if (scatter(P.scene, rng, 1u + depth, d, h, no, nd)) {
+                    stack[depth] = h.obj;
+                    ++depth;
+                    o = no; d = nd;
+                    done = false;
+                }
+            }
+            if (done) {
+                while (depth > 0) {  // tracer.rs:206-207 on the way back up
+                    --depth;
+                    pc = attenuation(P.scene, stack[depth]) * pc;
+                }
+                col = col + pc;      // tracer.rs:174
+                ++s;
+                alive = false;
+            }
         }
     }
 

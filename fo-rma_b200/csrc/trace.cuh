@@ -262,6 +262,15 @@ __device__ __forceinline__ void closest_hit(const SceneView& S, const float4* __
     h.t = 0.0f; h.p = f3(0.0f, 0.0f, 0.0f); h.n = f3(0.0f, 0.0f, 0.0f);
     h.closest = FLT_MAX; h.obj = -1;
     const float a = dot(d, d);  // sphere.rs:25
+    // Conservative whole-scene cull (brute-force scan only; the tree has its own padded root test):
+    // the line o + t d stays farther than R from the centre C of the bounding sphere of every finite
+    // sphere and triangle iff a (|oc|^2 - R^2) - (oc.d)^2 > 0.  The margin 2^-16 a (|oc|^2 + R^2) exceeds
+    // the rounding error of this expression (<= 2^-20 of the same magnitude) plus the largest miss
+    // distance at which sphere.rs:25-29's disc or the triangle test can still accept (same order), so
+    // nothing the scan would accept is skipped.  NaN / inf inputs make the comparison false -> full scan.
+    const float3 occ = o - f3(S.cull_center);
+    const float ccc = dot(occ, occ), bcc = dot(occ, d);
+    const bool culled = a * (ccc - S.cull_r2) - bcc * bcc > 1.52587890625e-05f * (a * (ccc + S.cull_r2));
     for (int sg = 0; sg < S.n_segments; ++sg) {
         const Segment g = S.segments[sg];
         Winner w;
@@ -269,9 +278,11 @@ __device__ __forceinline__ void closest_hit(const SceneView& S, const float4* __
         const bool tree = S.bvh_nodes != nullptr && g.sph_end + g.tri_end > g.sph_begin + g.tri_begin;
         const int sph_end = tree ? S.big_spheres : g.sph_end;
         const int tri_end = tree ? S.big_tris : g.tri_end;
-        for (int i = g.sph_begin; i < sph_end; ++i) try_sphere(S, sph, i, o, d, a, h, w);
-        for (int i = g.tri_begin; i < tri_end; ++i) try_triangle(S, tri, i, o, d, h, w);
-        if (tree) bvh_closest(S, sph, tri, o, d, a, h, w);
+        if (!culled) {
+            for (int i = g.sph_begin; i < sph_end; ++i) try_sphere(S, sph, i, o, d, a, h, w);
+            for (int i = g.tri_begin; i < tri_end; ++i) try_triangle(S, tri, i, o, d, h, w);
+            if (tree) bvh_closest(S, sph, tri, o, d, a, h, w);
+        }
         if (w.kind >= 0) {  // what the last accepting hit() left in the shared HitRecord
             h.t = h.closest;
             h.p = o + h.t * d;  // ray.rs:30-32
