@@ -267,6 +267,7 @@ int upload_scene(forma_rt* c) {
     v.segments = c->d_segments.p; v.material = c->d_material.p;
     v.kindmat = c->d_kindmat.p; v.ids = c->d_ids.p;
     v.n_segments = (int)segments.size();
+    v.seg0 = segments.empty() ? Segment{0, 0, 0, 0, -1} : segments[0];
     v.n_spheres = (int)ns; v.n_tris = (int)nt; v.n_planes = (int)np;
     v.bvh_nodes = nullptr;
 

@@ -40,6 +40,7 @@ struct SceneView {
     const float4* planes;
     const int* plane_obj;
     const Segment* segments;
+    Segment seg0;              // = segments[0], as a kernel-parameter (constant-bank) copy
     const float4* material;
     const int* kindmat;
     const int* ids;

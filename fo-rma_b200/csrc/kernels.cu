@@ -15,9 +15,9 @@ namespace forma {
 // x offset 8w (compact primary-ray footprint for the LBVH walk), lane -> (lane & 7, lane >> 3).
 constexpr int kTileW = 32, kTileH = 4, kBlock = 128;
 
-template <bool SMEM>
+template <int MODE>
 __device__ __forceinline__ void stage_scene(const SceneView& S, const float4*& sph, const float4*& tri) {
-    if constexpr (SMEM) {
+    if constexpr (MODE == kScanSmem) {
         extern __shared__ float4 smem_f4[];
         const int ns = S.n_spheres, nt3 = 3 * S.n_tris;
         for (int i = threadIdx.x; i < ns; i += blockDim.x) smem_f4[i] = S.spheres[i];
@@ -31,10 +31,10 @@ __device__ __forceinline__ void stage_scene(const SceneView& S, const float4*& s
     }
 }
 
-template <bool SMEM>
+template <int MODE>
 __global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ RenderParams P) {
     const float4 *sph, *tri;
-    stage_scene<SMEM>(P.scene, sph, tri);
+    stage_scene<MODE>(P.scene, sph, tri);
 
     __shared__ __align__(16) uint8_t tile_rgb[kTileH][kTileW * 3];
 
@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ 
             }
             HitState h;
             ++rays;
-            closest_hit<SMEM>(P.scene, sph, tri, o, d, h);
+            closest_hit<MODE>(P.scene, sph, tri, o, d, h);
             float3 pc = f3(0.0f, 0.0f, 0.0f);
             bool done = true;
             if (h.obj < 0) pc = sky(d);                      // tracer.rs:213-217
@@ -127,10 +127,10 @@ __global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ 
     }
 }
 
-template <bool SMEM>
+template <int MODE>
 __global__ void __launch_bounds__(kBlock) primary_hits_kernel(const __grid_constant__ PrimaryParams P) {
     const float4 *sph, *tri;
-    stage_scene<SMEM>(P.scene, sph, tri);
+    stage_scene<MODE>(P.scene, sph, tri);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t x = blockIdx.x * kTileW + warp * 8 + (lane & 7), y = blockIdx.y * kTileH + (lane >> 3);
     if (x >= P.width || y >= P.height) return;
@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(kBlock) primary_hits_kernel(const __grid_const
     float3 o, d;
     camera_ray(P.cam, rng, r0, u, v, true, o, d);
     HitState h;
-    closest_hit<SMEM>(P.scene, sph, tri, o, d, h);
+    closest_hit<MODE>(P.scene, sph, tri, o, d, h);
     const size_t i = (size_t)x + (size_t)y * P.width;
     P.prim_id[i] = h.obj >= 0 ? P.scene.ids[h.obj] : -1;
     P.t[i] = h.closest;
@@ -195,26 +195,30 @@ static dim3 tile_grid(uint32_t w, uint32_t h) { return dim3((w + kTileW - 1) / k
 
 cudaError_t launch_render(const RenderParams& P, cudaStream_t stream) {
     const dim3 grid = tile_grid(P.width, P.height);
-    if (P.scene.smem_bytes > 0) {
-        cudaError_t e = cudaFuncSetAttribute(render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if (P.scene.bvh_nodes) {
+        render_kernel<kTree><<<grid, kBlock, 0, stream>>>(P);
+    } else if (P.scene.smem_bytes > 0) {
+        cudaError_t e = cudaFuncSetAttribute(render_kernel<kScanSmem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              P.scene.smem_bytes);
         if (e != cudaSuccess) return e;
-        render_kernel<true><<<grid, kBlock, P.scene.smem_bytes, stream>>>(P);
+        render_kernel<kScanSmem><<<grid, kBlock, P.scene.smem_bytes, stream>>>(P);
     } else {
-        render_kernel<false><<<grid, kBlock, 0, stream>>>(P);
+        render_kernel<kScanGlobal><<<grid, kBlock, 0, stream>>>(P);
     }
     return cudaGetLastError();
 }
 
 cudaError_t launch_primary_hits(const PrimaryParams& P, cudaStream_t stream) {
     const dim3 grid = tile_grid(P.width, P.height);
-    if (P.scene.smem_bytes > 0) {
-        cudaError_t e = cudaFuncSetAttribute(primary_hits_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if (P.scene.bvh_nodes) {
+        primary_hits_kernel<kTree><<<grid, kBlock, 0, stream>>>(P);
+    } else if (P.scene.smem_bytes > 0) {
+        cudaError_t e = cudaFuncSetAttribute(primary_hits_kernel<kScanSmem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              P.scene.smem_bytes);
         if (e != cudaSuccess) return e;
-        primary_hits_kernel<true><<<grid, kBlock, P.scene.smem_bytes, stream>>>(P);
+        primary_hits_kernel<kScanSmem><<<grid, kBlock, P.scene.smem_bytes, stream>>>(P);
     } else {
-        primary_hits_kernel<false><<<grid, kBlock, 0, stream>>>(P);
+        primary_hits_kernel<kScanGlobal><<<grid, kBlock, 0, stream>>>(P);
     }
     return cudaGetLastError();
 }

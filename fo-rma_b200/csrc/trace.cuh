@@ -256,32 +256,43 @@ __device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __
     }
 }
 
-template <bool SMEM>
+// MODE selects what a kernel instantiation carries: the brute-force scan with the primitives staged
+// in shared memory, the same scan reading them through L1/L2, or the LBVH walk (plus the linear scan
+// of the few "big" primitives the tree leaves out).  The scan kernels contain no tree code at all.
+enum : int { kScanSmem = 0, kScanGlobal = 1, kTree = 2 };
+
+template <int MODE>
 __device__ __forceinline__ void closest_hit(const SceneView& S, const float4* __restrict__ sph,
                                             const float4* __restrict__ tri, float3 o, float3 d, HitState& h) {
     h.t = 0.0f; h.p = f3(0.0f, 0.0f, 0.0f); h.n = f3(0.0f, 0.0f, 0.0f);
     h.closest = FLT_MAX; h.obj = -1;
     const float a = dot(d, d);  // sphere.rs:25
-    // Conservative whole-scene cull (brute-force scan only; the tree has its own padded root test):
-    // the line o + t d stays farther than R from the centre C of the bounding sphere of every finite
-    // sphere and triangle iff a (|oc|^2 - R^2) - (oc.d)^2 > 0.  The margin 2^-16 a (|oc|^2 + R^2) exceeds
-    // the rounding error of this expression (<= 2^-20 of the same magnitude) plus the largest miss
-    // distance at which sphere.rs:25-29's disc or the triangle test can still accept (same order), so
-    // nothing the scan would accept is skipped.  NaN / inf inputs make the comparison false -> full scan.
+    // Conservative whole-scene cull: the line o + t d stays farther than R from the centre C of the
+    // bounding sphere of every finite sphere and triangle iff a (|oc|^2 - R^2) - (oc.d)^2 > 0.  The
+    // margin 2^-16 a (|oc|^2 + R^2) exceeds the rounding error of this expression (<= 2^-20 of the same
+    // magnitude) plus the largest miss distance at which sphere.rs:25-29's disc or the triangle test
+    // can still accept (same order), so nothing the scan would accept is skipped.  NaN / inf inputs
+    // make the comparison false -> full scan.
     const float3 occ = o - f3(S.cull_center);
     const float ccc = dot(occ, occ), bcc = dot(occ, d);
     const bool culled = a * (ccc - S.cull_r2) - bcc * bcc > 1.52587890625e-05f * (a * (ccc + S.cull_r2));
     for (int sg = 0; sg < S.n_segments; ++sg) {
-        const Segment g = S.segments[sg];
+        Segment g = S.seg0;  // the first (usually only) segment travels in the constant bank
+        if (sg > 0) g = S.segments[sg];
         Winner w;
-        // With an LBVH the tree holds all but the first big_* primitives of the (single) run
-        const bool tree = S.bvh_nodes != nullptr && g.sph_end + g.tri_end > g.sph_begin + g.tri_begin;
-        const int sph_end = tree ? S.big_spheres : g.sph_end;
-        const int tri_end = tree ? S.big_tris : g.tri_end;
+        int sph_end = g.sph_end, tri_end = g.tri_end;
+        bool tree = false;
+        if constexpr (MODE == kTree) {
+            // the tree holds all but the first big_* primitives of the (single) run
+            tree = g.sph_end + g.tri_end > g.sph_begin + g.tri_begin;
+            if (tree) { sph_end = S.big_spheres; tri_end = S.big_tris; }
+        }
         if (!culled) {
             for (int i = g.sph_begin; i < sph_end; ++i) try_sphere(S, sph, i, o, d, a, h, w);
             for (int i = g.tri_begin; i < tri_end; ++i) try_triangle(S, tri, i, o, d, h, w);
-            if (tree) bvh_closest(S, sph, tri, o, d, a, h, w);
+            if constexpr (MODE == kTree) {
+                if (tree) bvh_closest(S, sph, tri, o, d, a, h, w);
+            }
         }
         if (w.kind >= 0) {  // what the last accepting hit() left in the shared HitRecord
             h.t = h.closest;
@@ -371,35 +382,6 @@ __device__ __forceinline__ float3 sky(float3 d) {
     float y = d.y / length(d);  // unit_vector().y
     float t = 0.5f * (y + 1.0f);
     return (1.0f - t) * f3(1.0f, 1.0f, 1.0f) + t * f3(0.5f, 0.7f, 1.0f);
-}
-
-// get_color (tracer.rs:189-219), recursion unrolled: the attenuations are multiplied innermost
-// first, exactly as the recursion returns them, so the list indices of the hit objects are kept on
-// a small per-path stack.  `rays` counts closest-hit queries.
-template <bool SMEM>
-__device__ __forceinline__ float3 get_color(const SceneView& S, const float4* sph, const float4* tri,
-                                            const PathRng& rng, float3 o, float3 d, uint32_t max_depth,
-                                            uint32_t& rays) {
-    int stack[kMaxDepthCap];
-    uint32_t depth = 0;
-    float3 col;
-    for (;;) {
-        HitState h;
-        ++rays;
-        closest_hit<SMEM>(S, sph, tri, o, d, h);
-        if (h.obj < 0) { col = sky(d); break; }
-        if (depth >= max_depth) { col = f3(0.0f, 0.0f, 0.0f); break; }  // tracer.rs:205,208-209
-        float3 no, nd;
-        if (!scatter(S, rng, 1u + depth, d, h, no, nd)) { col = f3(0.0f, 0.0f, 0.0f); break; }
-        stack[depth] = h.obj;
-        ++depth;
-        o = no; d = nd;
-    }
-    while (depth > 0) {  // tracer.rs:206-207 on the way back up
-        --depth;
-        col = attenuation(S, stack[depth]) * col;
-    }
-    return col;
 }
 
 // Rust `as u8` (tracer.rs:74-76,181-183): truncate, saturate, NaN -> 0
