@@ -4,6 +4,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <stdexcept>
@@ -55,6 +56,7 @@ struct DevBuf {
 
 constexpr int kSmemStageLimit = 96 * 1024;   // stage spheres+tris in shared memory up to this size
 constexpr uint32_t kBvhThreshold = 16;       // ACCEL_AUTO: LBVH at or above this many spheres + triangles
+constexpr size_t kRadBudget = 1ull << 30;    // tree mode: bytes of per-path radiance kept between trace and accumulate
 
 }  // namespace
 
@@ -68,6 +70,10 @@ struct forma_rt {
     forma::Scene scene;
     bool scene_dirty = true;
     bool stats_pending = false;
+    // render_tree_kernel tuning (FORMA_RT_REFILL / FORMA_RT_LEAF_BATCH / FORMA_RT_WALK_MODE override; not part of the ABI)
+    uint32_t refill = 16;     // lanes idle before a warp stops walking to refill them
+    uint32_t leaf_batch = 8;  // walk_mode 1: lanes waiting at a leaf before the warp runs the primitive tests
+    uint32_t walk_mode = 0;   // 0: while-while steps, 1: one node per iteration with batched leaves
     uint32_t frame = 0;  // update() call counter -> sample index of the interactive frame
 
     // packed scene (host copies kept for re-upload after set_object)
@@ -82,6 +88,8 @@ struct forma_rt {
     DevBuf<float4> d_sum;
     DevBuf<int32_t> d_prim;
     DevBuf<float> d_t;
+    DevBuf<float4> d_rad, d_acc;      // tree mode: per-path radiance of a chunk of samples, in-order running sum
+    DevBuf<unsigned int> d_job;       // tree mode: job queue head
     unsigned long long* d_rays = nullptr;
     unsigned long long* h_rays = nullptr;  // pinned
 
@@ -97,6 +105,7 @@ struct forma_rt {
         d_spheres.release(); d_tris.release(); d_planes.release(); d_material.release();
         d_sphere_obj.release(); d_tri_obj.release(); d_plane_obj.release(); d_kindmat.release(); d_ids.release();
         d_segments.release(); d_rgb.release(); d_sum.release(); d_prim.release(); d_t.release();
+        d_rad.release(); d_acc.release(); d_job.release();
         bvh.release();
         if (d_rays) cudaFree(d_rays);
         if (h_rays) cudaFreeHost(h_rays);
@@ -291,7 +300,7 @@ int upload_scene(forma_rt* c) {
         v.cull_r2 = (finite && ns + nt > 0 && std::isfinite(r2)) ? r2 : INFINITY;
         if (!(v.cull_r2 < INFINITY)) v.cull_center[0] = v.cull_center[1] = v.cull_center[2] = 0.0f;
     }
-    v.bvh_prim = nullptr; v.big_spheres = 0; v.big_tris = 0;
+    v.bvh_prim = nullptr; v.big_spheres = 0; v.big_tris = 0; v.tree_seg = 0;
     c->stats.bvh_nodes = 0;
     c->stats.accel_in_use = FORMA_RT_ACCEL_BRUTE;
     if (use_bvh) {
@@ -300,6 +309,8 @@ int upload_scene(forma_rt* c) {
         if (e != cudaSuccess) return fail(FORMA_RT_ECUDA, std::string("LBVH build: ") + cudaGetErrorString(e));
         v.bvh_nodes = c->bvh.nodes; v.bvh_prim = c->bvh.prim;
         v.big_spheres = bin.big_spheres; v.big_tris = bin.big_tris;
+        for (size_t k = 0; k < segments.size(); ++k)
+            if (segments[k].sph_end > segments[k].sph_begin || segments[k].tri_end > segments[k].tri_begin) v.tree_seg = (int)k;
         v.bvh_center[0] = bc[0]; v.bvh_center[1] = bc[1]; v.bvh_center[2] = bc[2];
         v.bvh_r2 = br2; v.bvh_eps = beps;
         c->stats.bvh_nodes = (uint32_t)(bin.count - 1);
@@ -381,6 +392,18 @@ int forma_rt_create(const forma_rt_options* opts, uint32_t width, uint32_t heigh
     c->stats.sm_count = (uint32_t)c->sm_count;
     c->stats.sm_clock_khz = (uint32_t)c->clock_khz;
 
+    if (const char* r = std::getenv("FORMA_RT_REFILL")) {  // tuning knob, not part of the ABI
+        const int v = std::atoi(r);
+        if (v >= 1 && v <= 32) c->refill = (uint32_t)v;
+    }
+    if (const char* r = std::getenv("FORMA_RT_LEAF_BATCH")) {
+        const int v = std::atoi(r);
+        if (v >= 1 && v <= 32) c->leaf_batch = (uint32_t)v;
+    }
+    if (const char* r = std::getenv("FORMA_RT_WALK_MODE")) {
+        const int v = std::atoi(r);
+        if (v == 0 || v == 1) c->walk_mode = (uint32_t)v;
+    }
     // Scene::new (scene.rs:10-15): Camera::new + get_simple_scene
     c->scene.camera = forma::Camera::create(width, height);
     c->scene.objects = forma::builtin_scene(0);
@@ -525,11 +548,23 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
     P.spp = spp; P.sample_offset = sample_offset; P.max_depth = max_depth; P.flags = flags;
     P.rk.expand(c->seed);
     P.rgb = d_rgb; P.sum = d_sum; P.rays = c->d_rays;
+    if (P.scene.bvh_nodes) {  // tree mode: rad holds a chunk of samples of the frame, <= kRadBudget bytes
+        const size_t npix = (size_t)c->width * c->height;
+        size_t chunk = kRadBudget / (npix * sizeof(float4));
+        chunk = std::max<size_t>(1, std::min<size_t>({chunk, spp, 64}));
+        CU_TRY(c->d_rad.ensure(npix * chunk));
+        CU_TRY(c->d_acc.ensure(npix));
+        CU_TRY(c->d_job.ensure(1));
+        P.rad = c->d_rad.p; P.acc = c->d_acc.p; P.job_counter = c->d_job.p;
+        P.rad_chunk = (uint32_t)chunk;
+        P.refill = c->refill; P.leaf_batch = c->leaf_batch; P.walk_mode = c->walk_mode;
+    }
+    uint32_t launches = 0;
     CU_TRY(cudaMemsetAsync(c->d_rays, 0, sizeof(unsigned long long), stream));
     CU_TRY(cudaEventRecord(c->ev_k0, stream));
-    CU_TRY(forma::launch_render(P, stream));
+    CU_TRY(forma::launch_render(P, c->sm_count, stream, &launches));
     CU_TRY(cudaEventRecord(c->ev_k1, stream));
-    c->stats.gpu_launches = 1;
+    c->stats.gpu_launches = launches;
     c->stats.paths = (uint64_t)c->width * c->height * spp;
     c->stats_pending = true;  // ray counter + kernel time are read back by whoever synchronises
     return FORMA_RT_OK;

@@ -48,6 +48,7 @@ struct SceneView {
     const float4* bvh_nodes;   // 4 float4 per internal node: see lbvh.cu
     const int* bvh_prim;       // unified primitive index (< n_spheres: sphere) of sorted leaf l
     int big_spheres, big_tris; // with a tree: the first big_* packed primitives are scanned linearly
+    int tree_seg;              // with a tree: index of the one segment that holds spheres / triangles
     float bvh_center[3];       // bounding sphere of everything the tree indexes
     float bvh_r2;              // its radius squared
     float bvh_eps;             // absolute box pad: 2^-16 x scene scale
@@ -78,6 +79,15 @@ struct RenderParams {
     uint8_t* rgb;              // nullable
     float4* sum;               // nullable
     unsigned long long* rays;  // device counter
+    // ---- tree mode only (render_tree_kernel + accumulate_kernel, kernels.cu) ----
+    float4* rad;               // [chunk sample][pixel] radiance of the finished paths of one chunk
+    float4* acc;               // [pixel] running in-order sum across chunks
+    unsigned int* job_counter; // next (pixel, sample) job of the chunk
+    uint32_t rad_chunk;        // capacity of `rad` in samples
+    uint32_t chunk_base, chunk_k; // samples [chunk_base, chunk_base + chunk_k) are traced by this launch
+    uint32_t walk_mode;        // 0: while-while steps, 1: one node per iteration with batched leaves
+    uint32_t leaf_batch;       // walk_mode 1: lanes waiting at a leaf before the warp runs the primitive tests
+    uint32_t refill;           // refill a warp's finished lanes once this many are idle
 };
 
 struct PrimaryParams {

@@ -31,6 +31,35 @@ __device__ __forceinline__ void stage_scene(const SceneView& S, const float4*& s
     }
 }
 
+// tracer.rs:177-184 for one pixel per thread: f32 sum out, and / or average in linear space, sqrt
+// gamma, (c * 255.0) as u8 — the RGB8 tile staged in shared memory and stored as coalesced words.
+__device__ __forceinline__ void write_out(const RenderParams& P, float3 col, uint32_t x, uint32_t y, int lx, int ly,
+                                          bool live, uint8_t (*tile_rgb)[kTileW * 3]) {
+    if (P.sum && live) P.sum[(size_t)x + (size_t)y * P.width] = make_float4(col.x, col.y, col.z, (float)P.spp);
+
+    if (P.rgb) {
+        // tracer.rs:177-184: average in linear space, sqrt gamma, (c * 255.0) as u8
+        float3 c = col / (float)P.spp;
+        const uint32_t r = as_u8(sqrtf(c.x) * 255.0f), g = as_u8(sqrtf(c.y) * 255.0f), b = as_u8(sqrtf(c.z) * 255.0f);
+        const bool full_tile = (blockIdx.x + 1) * kTileW <= P.width && (blockIdx.y + 1) * kTileH <= P.height &&
+                               (P.width * 3u) % 4u == 0;
+        if (full_tile) {  // stage 4 rows x 96 bytes, write them as 96 coalesced 32-bit words
+            tile_rgb[ly][lx * 3 + 0] = (uint8_t)r;
+            tile_rgb[ly][lx * 3 + 1] = (uint8_t)g;
+            tile_rgb[ly][lx * 3 + 2] = (uint8_t)b;
+            __syncthreads();
+            if (threadIdx.x < kTileH * 24) {
+                const int row = threadIdx.x / 24, word = threadIdx.x % 24;
+                const size_t byte = ((size_t)(blockIdx.y * kTileH + row) * P.width + (size_t)blockIdx.x * kTileW) * 3;
+                reinterpret_cast<uint32_t*>(P.rgb + byte)[word] = reinterpret_cast<const uint32_t*>(tile_rgb[row])[word];
+            }
+        } else if (live) {
+            uint8_t* px = P.rgb + ((size_t)x + (size_t)y * P.width) * 3;
+            px[0] = (uint8_t)r; px[1] = (uint8_t)g; px[2] = (uint8_t)b;
+        }
+    }
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ RenderParams P) {
     const float4 *sph, *tri;
@@ -102,27 +131,188 @@ __global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ 
     uint32_t wr = __reduce_add_sync(0xffffffffu, rays);
     if (lane == 0 && wr) atomicAdd(P.rays, (unsigned long long)wr);
 
-    if (P.sum && live) P.sum[(size_t)x + (size_t)y * P.width] = make_float4(col.x, col.y, col.z, (float)P.spp);
+    write_out(P, col, x, y, lx, ly, live, tile_rgb);
+}
 
-    if (P.rgb) {
-        // tracer.rs:177-184: average in linear space, sqrt gamma, (c * 255.0) as u8
-        float3 c = col / (float)P.spp;
-        const uint32_t r = as_u8(sqrtf(c.x) * 255.0f), g = as_u8(sqrtf(c.y) * 255.0f), b = as_u8(sqrtf(c.z) * 255.0f);
-        const bool full_tile = (blockIdx.x + 1) * kTileW <= P.width && (blockIdx.y + 1) * kTileH <= P.height &&
-                               (P.width * 3u) % 4u == 0;
-        if (full_tile) {  // stage 4 rows x 96 bytes, write them as 96 coalesced 32-bit words
-            tile_rgb[ly][lx * 3 + 0] = (uint8_t)r;
-            tile_rgb[ly][lx * 3 + 1] = (uint8_t)g;
-            tile_rgb[ly][lx * 3 + 2] = (uint8_t)b;
-            __syncthreads();
-            if (threadIdx.x < kTileH * 24) {
-                const int row = threadIdx.x / 24, word = threadIdx.x % 24;
-                const size_t byte = ((size_t)(blockIdx.y * kTileH + row) * P.width + (size_t)blockIdx.x * kTileW) * 3;
-                reinterpret_cast<uint32_t*>(P.rgb + byte)[word] = reinterpret_cast<const uint32_t*>(tile_rgb[row])[word];
+// Tree-mode path tracer (persistent warps).  Two things make a pixel-per-thread loop slow on scenes
+// with real bounces: rays of one warp need very different numbers of LBVH nodes, and pixels of one
+// tile need very different numbers of rays (sky next to a cluster of spheres).  So here
+//  * the (pixel, sample) pairs of a chunk of samples are JOBS in one global queue; a lane draws its
+//    next job when its path ends, so no lane idles while work is left anywhere on the GPU.  Jobs
+//    are ordered 8x4-pixel tile -> sample -> pixel, so a warp's primary rays stay coherent;
+//  * a finished path writes its radiance to rad[sample in chunk][pixel]; accumulate_kernel then
+//    adds every pixel's samples IN SAMPLE ORDER - the same f32 chain as tracer.rs:170-175, so the
+//    sums stay bit-identical to the flat loop and to the CPU restatement.  Cost: 32 B of HBM traffic per
+//    path, nothing next to the thousands of instructions a bouncing path takes;
+//  * every lane is a small state machine so that a warp never waits on its slowest ray:
+//      kShade    winner -> HitRecord, trailing planes, scatter / sky / termination (tracer.rs:201-217)
+//      kNewPath  draw a job, generate its camera ray                      (tracer.rs:171-173)
+//      kStart    planes that precede the tree's run, the linear "big" primitives, walk_begin
+//      kWalk     resumable LBVH walk
+//    The warp walks until `refill` lanes have finished their walk (or none is walking), then those
+//    lanes shade, scatter or draw their next job and rejoin.
+enum : int { kNewPath = 0, kStart = 1, kWalk = 2, kShade = 3 };
+
+__global__ void __launch_bounds__(kBlock) render_tree_kernel(const __grid_constant__ RenderParams P) {
+    const SceneView& S = P.scene;
+    const float4 *sph = S.spheres, *tri = S.tris;
+    const int lane = threadIdx.x & 31;
+    constexpr unsigned kFull = 0xffffffffu;
+    const uint32_t tiles_x = (P.width + 7) / 8, tiles_y = (P.height + 3) / 4;
+    const uint32_t n_jobs = tiles_x * tiles_y * P.chunk_k * 32u;  // < 2^32: checked by the launcher
+    const float fw = (float)P.width, fh = (float)P.height;
+    const bool no_jitter = P.flags & FORMA_RT_NO_JITTER, pinhole = P.flags & FORMA_RT_PINHOLE;
+
+    uint32_t rays = 0;
+    int astack[kMaxDepthCap];   // list indices of the hit objects: attenuations multiply innermost first
+    int2 wstack[64];            // walk stack: (child, entry distance)
+    PathRng rng{P.rk, 0u, 0u};
+    uint32_t depth = 0, slot = 0;  // slot: where this path's radiance goes in `rad`
+    int phase = kNewPath;
+    bool lane_done = false;
+    float3 o = f3(0.0f, 0.0f, 0.0f), d = o;
+    float a = 0.0f;
+    HitState h;
+    Winner w;
+    Walk W;
+    h.t = 0.0f; h.p = o; h.n = o; h.closest = FLT_MAX; h.obj = -1;
+    W.ix = W.iy = W.iz = W.ox = W.oy = W.oz = W.coef = 0.0f; W.node = kWalkDone; W.sp = 0;
+
+    for (;;) {
+        // ---- A. shade the rays whose walk has finished
+        if (phase == kShade) {
+            for (int sg = S.tree_seg; sg < S.n_segments; ++sg) {
+                Segment g = S.seg0;
+                if (sg > 0) g = S.segments[sg];
+                if (sg == S.tree_seg) finalize_winner(sph, tri, o, d, w, h);
+                if (g.plane >= 0) plane_hit(S, g.plane, o, d, h);
             }
-        } else if (live) {
-            uint8_t* px = P.rgb + ((size_t)x + (size_t)y * P.width) * 3;
-            px[0] = (uint8_t)r; px[1] = (uint8_t)g; px[2] = (uint8_t)b;
+            float3 pc = f3(0.0f, 0.0f, 0.0f);
+            bool done = true;
+            if (h.obj < 0) pc = sky(d);                      // tracer.rs:213-217
+            else if (depth < P.max_depth) {                  // tracer.rs:205
+                float3 no, nd;
+                if (scatter(S, rng, 1u + depth, d, h, no, nd)) {
+                    astack[depth] = h.obj;
+                    ++depth;
+                    o = no; d = nd;
+                    done = false;
+                }
+            }
+            phase = kStart;
+            if (done) {
+                while (depth > 0) {  // tracer.rs:206-207 on the way back up
+                    --depth;
+                    pc = attenuation(S, astack[depth]) * pc;
+                }
+                P.rad[slot] = make_float4(pc.x, pc.y, pc.z, 1.0f);
+                phase = kNewPath;
+            }
+        }
+        // ---- B. one queue transaction for all lanes of the warp that need a job
+        const unsigned need = __ballot_sync(kFull, phase == kNewPath && !lane_done);
+        if (need != 0u) {
+            unsigned base = 0;
+            if (lane == __ffs(need) - 1) base = atomicAdd(P.job_counter, (unsigned)__popc(need));
+            base = __shfl_sync(kFull, base, __ffs(need) - 1);
+            if (phase == kNewPath && !lane_done) {
+                // ---- C. decode the job, generate its camera ray
+                uint32_t job = base + __popc(need & ((1u << lane) - 1u));
+                uint32_t jx = 0, jy = 0, k = 0;
+                bool have = false;
+                while (job < n_jobs) {  // jobs of pixels outside the image (partial edge tiles) are skipped
+                    const uint32_t t = job & 31u, rest = job >> 5;
+                    k = rest % P.chunk_k;
+                    const uint32_t tile = rest / P.chunk_k;
+                    jx = (tile % tiles_x) * 8u + (t & 7u); jy = (tile / tiles_x) * 4u + (t >> 3);
+                    if (jx < P.width && jy < P.height) { have = true; break; }
+                    job = atomicAdd(P.job_counter, 1u);
+                }
+                if (!have) lane_done = true;
+                else {
+                    rng.pixel = jx + jy * P.width;
+                    rng.sample = P.sample_offset + P.chunk_base + k;
+                    slot = k * (P.width * P.height) + rng.pixel;
+                    Rand4 r0 = rng.block(0, 0);
+                    if (no_jitter) { r0.x = 0.5f; r0.y = 0.5f; }
+                    const float u = ((float)jx + r0.x) / fw;                    // tracer.rs:171
+                    const float v = ((float)(P.height - jy) + r0.y) / fh;       // tracer.rs:172 (Q1: height - y)
+                    camera_ray(P.cam, rng, r0, u, v, pinhole, o, d);
+                    depth = 0;
+                    phase = kStart;
+                }
+            }
+        }
+        // ---- D. tracer.rs:190-194, then everything the scan meets before the tree
+        if (phase == kStart) {
+            ++rays;
+            h.t = 0.0f; h.p = f3(0.0f, 0.0f, 0.0f); h.n = h.p;
+            h.closest = FLT_MAX; h.obj = -1;
+            w = Winner{};
+            a = dot(d, d);  // sphere.rs:25
+            for (int sg = 0; sg < S.tree_seg; ++sg) {  // plane-only segments in front of the run
+                const Segment g = S.segments[sg];
+                if (g.plane >= 0) plane_hit(S, g.plane, o, d, h);
+            }
+            phase = kShade;
+            if (!scene_culled(S, o, d, a)) {
+                for (int i = 0; i < S.big_spheres; ++i) try_sphere(S, sph, i, o, d, a, h, w);
+                for (int i = 0; i < S.big_tris; ++i) try_triangle(S, tri, i, o, d, h, w);
+                walk_begin(S, o, d, W);
+                phase = kWalk;
+            }
+        }
+        if (__ballot_sync(kFull, !lane_done) == 0u) break;  // the queue is empty and every lane has finished
+        // ---- E. walk until enough lanes are idle to be worth refilling
+        if (P.walk_mode == 0u) {
+            for (;;) {
+                if (phase == kWalk && !walk_step(S, sph, tri, o, d, a, W, wstack, h, w)) phase = kShade;
+                const unsigned walking = __ballot_sync(kFull, phase == kWalk);
+                const unsigned idle = __ballot_sync(kFull, !lane_done && phase != kWalk);
+                if (walking == 0u || __popc(idle) >= (int)P.refill) break;
+            }
+        } else {
+            // one node per lane and iteration; lanes that reach a leaf wait there until `leaf_batch` of
+            // them can test their primitives together (or no lane is at an internal node)
+            for (;;) {
+                if (phase == kWalk && W.node >= 0) walk_inner(S, W, wstack, h.closest);
+                const bool at_leaf = phase == kWalk && W.node < 0 && W.node != kWalkDone;
+                const unsigned leaves = __ballot_sync(kFull, at_leaf);
+                const unsigned inner = __ballot_sync(kFull, phase == kWalk && W.node >= 0);
+                if (leaves != 0u && (__popc(leaves) >= (int)P.leaf_batch || inner == 0u)) {
+                    if (at_leaf) walk_leaf(S, sph, tri, o, d, a, W, wstack, h, w);
+                }
+                if (phase == kWalk && W.node == kWalkDone) phase = kShade;
+                const unsigned walking = __ballot_sync(kFull, phase == kWalk);
+                const unsigned idle = __ballot_sync(kFull, !lane_done && phase != kWalk);
+                if (walking == 0u || __popc(idle) >= (int)P.refill) break;
+            }
+        }
+    }
+
+    // closest-hit query count: one atomic per warp
+    uint32_t wr = __reduce_add_sync(kFull, rays);
+    if (lane == 0 && wr) atomicAdd(P.rays, (unsigned long long)wr);
+}
+
+// tracer.rs:170-184 for tree mode: acc[p] += rad[0][p], rad[1][p], ... in sample order; after the last
+// chunk the f32 sum and / or the sqrt-gamma RGB8 pixel are written out.
+__global__ void accumulate_kernel(const __grid_constant__ RenderParams P, int first, int last) {
+    const size_t npix = (size_t)P.width * P.height;
+    for (size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x; p < npix; p += (size_t)gridDim.x * blockDim.x) {
+        float3 col = f3(0.0f, 0.0f, 0.0f);
+        if (!first) { const float4 c = P.acc[p]; col = f3(c.x, c.y, c.z); }
+        for (uint32_t k = 0; k < P.chunk_k; ++k) {
+            const float4 r = P.rad[k * npix + p];
+            col = col + f3(r.x, r.y, r.z);  // tracer.rs:174
+        }
+        if (!last) { P.acc[p] = make_float4(col.x, col.y, col.z, 0.0f); continue; }
+        if (P.sum) P.sum[p] = make_float4(col.x, col.y, col.z, (float)P.spp);
+        if (P.rgb) {
+            const float3 c = col / (float)P.spp;
+            P.rgb[3 * p + 0] = (uint8_t)as_u8(sqrtf(c.x) * 255.0f);
+            P.rgb[3 * p + 1] = (uint8_t)as_u8(sqrtf(c.y) * 255.0f);
+            P.rgb[3 * p + 2] = (uint8_t)as_u8(sqrtf(c.z) * 255.0f);
         }
     }
 }
@@ -193,11 +383,37 @@ __global__ void reduce_tonemap_kernel(const __grid_constant__ PeerPtrs peers, in
 // ---- launchers -------------------------------------------------------------------------------------
 static dim3 tile_grid(uint32_t w, uint32_t h) { return dim3((w + kTileW - 1) / kTileW, (h + kTileH - 1) / kTileH); }
 
-cudaError_t launch_render(const RenderParams& P, cudaStream_t stream) {
+static int stream_grid(uint64_t n, int sm_count);
+
+// Tree mode: chunks of at most P.rad_chunk samples; per chunk one persistent trace launch (as many
+// CTAs as fit on the device at once) and one in-order accumulate launch.
+static cudaError_t launch_render_tree(RenderParams P, int sm_count, cudaStream_t stream, uint32_t* launches) {
+    if (!P.rad || !P.acc || !P.job_counter || P.rad_chunk == 0) return cudaErrorInvalidValue;
+    const uint64_t tiles = (uint64_t)((P.width + 7) / 8) * ((P.height + 3) / 4);
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_tree_kernel, kBlock, 0);
+    if (e != cudaSuccess) return e;
+    const int grid = sm_count * (per_sm > 0 ? per_sm : 1);
+    const size_t npix = (size_t)P.width * P.height;
+    for (uint32_t base = 0; base < P.spp; base += P.rad_chunk) {
+        uint32_t k = P.spp - base < P.rad_chunk ? P.spp - base : P.rad_chunk;
+        while (tiles * k * 32u >= (1ull << 32)) k = (k + 1) / 2;  // job indices are 32-bit
+        P.chunk_base = base; P.chunk_k = k;
+        if ((e = cudaMemsetAsync(P.job_counter, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
+        render_tree_kernel<<<grid, kBlock, 0, stream>>>(P);
+        accumulate_kernel<<<stream_grid(npix, sm_count), 256, 0, stream>>>(P, base == 0, base + k >= P.spp);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        *launches += 2;
+        if (k < P.rad_chunk && base + k < P.spp) base -= P.rad_chunk - k;  // a halved chunk: continue right after it
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_render(const RenderParams& P, int sm_count, cudaStream_t stream, uint32_t* launches) {
+    *launches = 0;
+    if (P.scene.bvh_nodes) return launch_render_tree(P, sm_count, stream, launches);
     const dim3 grid = tile_grid(P.width, P.height);
-    if (P.scene.bvh_nodes) {
-        render_kernel<kTree><<<grid, kBlock, 0, stream>>>(P);
-    } else if (P.scene.smem_bytes > 0) {
+    if (P.scene.smem_bytes > 0) {
         cudaError_t e = cudaFuncSetAttribute(render_kernel<kScanSmem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              P.scene.smem_bytes);
         if (e != cudaSuccess) return e;
@@ -205,6 +421,7 @@ cudaError_t launch_render(const RenderParams& P, cudaStream_t stream) {
     } else {
         render_kernel<kScanGlobal><<<grid, kBlock, 0, stream>>>(P);
     }
+    *launches = 1;
     return cudaGetLastError();
 }
 

@@ -194,6 +194,57 @@ __device__ __forceinline__ void try_triangle(const SceneView& S, const float4* _
     }
 }
 
+// What the last accepting hit() of a segment left in the shared HitRecord (sphere.rs:33-36,42-45).
+__device__ __forceinline__ void finalize_winner(const float4* __restrict__ sph, const float4* __restrict__ tri,
+                                                float3 o, float3 d, const Winner& w, HitState& h) {
+    if (w.kind >= 0) {
+        h.t = h.closest;
+        h.p = o + h.t * d;  // ray.rs:30-32
+        if (w.kind == 0) {
+            const float4 s = sph[w.slot];
+            h.n = (h.p - xyz(s)) / s.w;  // sphere.rs:35,44
+        } else {
+            float3 n = f3(tri[3 * w.slot].w, tri[3 * w.slot + 1].w, tri[3 * w.slot + 2].w);
+            if (dot(d, n) > 0.0f) n = n * -1.0f;
+            h.n = n;
+        }
+        h.obj = w.obj;
+    }
+}
+
+// Plane::hit (plane.rs:24-44).  Q4: the range test is on denom, never on t; Q5: t and p are written
+// before the extent test and stay clobbered on a reject.
+__device__ __forceinline__ void plane_hit(const SceneView& S, int k, float3 o, float3 d, HitState& h) {
+    const float3 position = xyz(S.planes[3 * k]);
+    const float3 orientation = xyz(S.planes[3 * k + 1]);
+    const float3 size = xyz(S.planes[3 * k + 2]);
+    float denom = dot(orientation, d);
+    if (denom > kTMin && denom < h.closest) {
+        float3 plane_to_ray = position - o;
+        h.t = dot(plane_to_ray, orientation) / denom;
+        h.p = o + h.t * d;
+        if (h.p.x > position.x - size.x && h.p.x < position.x + size.x &&
+            h.p.y > position.y - size.y && h.p.y < position.y + size.y &&
+            h.p.z > position.z - size.z && h.p.z < position.z + size.z) {
+            h.n = orientation * -1.0f;
+            h.closest = h.t;  // tracer.rs:197
+            h.obj = S.plane_obj[k];
+        }
+    }
+}
+
+// Conservative whole-scene cull: the line o + t d stays farther than R from the centre C of the
+// bounding sphere of every finite sphere and triangle iff a (|oc|^2 - R^2) - (oc.d)^2 > 0.  The margin
+// 2^-16 a (|oc|^2 + R^2) exceeds the rounding error of this expression (<= 2^-20 of the same magnitude)
+// plus the largest miss distance at which sphere.rs:25-29's disc or the triangle test can still accept
+// (same order), so nothing the scan would accept is skipped.  NaN / inf inputs make the comparison
+// false -> full scan.
+__device__ __forceinline__ bool scene_culled(const SceneView& S, float3 o, float3 d, float a) {
+    const float3 oc = o - f3(S.cull_center);
+    const float cc = dot(oc, oc), b = dot(oc, d);
+    return a * (cc - S.cull_r2) - b * b > 1.52587890625e-05f * (a * (cc + S.cull_r2));
+}
+
 // LBVH walk over the primitives the tree indexes (lbvh.cu).  Exactness: a child box is visited iff
 // the ray's interval through the PADDED box reaches [0, closest]; the pad
 //     coef(ray) * q(child) + eps,   coef = 2^-19 (|o - C|^2 + R^2),  q = max 1/r below the child
@@ -256,6 +307,91 @@ __device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __
     }
 }
 
+// ---- resumable LBVH walk (render_tree_kernel) ------------------------------------------------------
+// The same padded walk as bvh_closest, cut into steps so that a warp can stop walking when enough
+// of its lanes have finished, refill those lanes with their next ray, and resume ("while-while"
+// traversal with ray regeneration).  One step = descend through internal nodes until a leaf is the
+// current node, test that leaf's primitive, pop.  Stack entries carry the entry distance of the
+// pushed child so a pop skips subtrees that the hits found meanwhile have put out of range.
+constexpr int kWalkDone = (int)0x80000000;  // never a leaf code: leaves are ~l with l < 2^31 - 1
+
+struct Walk {
+    float ix, iy, iz, ox, oy, oz;  // 1/d and -o/d
+    float coef;                    // 2^-19 (|o - C|^2 + R^2): the pad scale of this ray
+    int node;                      // >= 0 internal, < 0 leaf ~node, kWalkDone
+    int sp;
+};
+
+__device__ __forceinline__ void walk_begin(const SceneView& S, float3 o, float3 d, Walk& W) {
+    const float huge = 1e30f;
+    W.ix = fabsf(d.x) < 1e-30f ? copysignf(huge, d.x) : 1.0f / d.x;
+    W.iy = fabsf(d.y) < 1e-30f ? copysignf(huge, d.y) : 1.0f / d.y;
+    W.iz = fabsf(d.z) < 1e-30f ? copysignf(huge, d.z) : 1.0f / d.z;
+    W.ox = -o.x * W.ix; W.oy = -o.y * W.iy; W.oz = -o.z * W.iz;
+    const float3 oc = o - f3(S.bvh_center);
+    W.coef = 1.9073486e-6f * (dot(oc, oc) + S.bvh_r2);  // 2^-19
+    W.node = 0;
+    W.sp = 0;
+}
+
+__device__ __forceinline__ int walk_pop(Walk& W, const int2* stack, float closest) {
+    while (W.sp > 0) {
+        const int2 e = stack[--W.sp];
+        if (__int_as_float(e.y) <= closest) return e.x;  // <=: an equal t with a smaller list index still wins
+    }
+    return kWalkDone;
+}
+
+// One internal node: test both child boxes, descend into the nearer hit child (pushing the other) or pop.
+__device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, int2* stack, float closest) {
+    const int node = W.node;
+    const float eps = S.bvh_eps;
+    const float4 n0 = __ldg(S.bvh_nodes + 4 * node), n1 = __ldg(S.bvh_nodes + 4 * node + 1);
+    const float4 n2 = __ldg(S.bvh_nodes + 4 * node + 2), n3 = __ldg(S.bvh_nodes + 4 * node + 3);
+    const float padL = __fmaf_rn(W.coef, n3.z, eps), padR = __fmaf_rn(W.coef, n3.w, eps);
+    float t0 = __fmaf_rn(n0.x - padL, W.ix, W.ox), t1 = __fmaf_rn(n0.w + padL, W.ix, W.ox);
+    float nearL = fminf(t0, t1), farL = fmaxf(t0, t1);
+    t0 = __fmaf_rn(n0.y - padL, W.iy, W.oy); t1 = __fmaf_rn(n1.x + padL, W.iy, W.oy);
+    nearL = fmaxf(nearL, fminf(t0, t1)); farL = fminf(farL, fmaxf(t0, t1));
+    t0 = __fmaf_rn(n0.z - padL, W.iz, W.oz); t1 = __fmaf_rn(n1.y + padL, W.iz, W.oz);
+    nearL = fmaxf(fmaxf(nearL, fminf(t0, t1)), 0.0f); farL = fminf(fminf(farL, fmaxf(t0, t1)), closest);
+    t0 = __fmaf_rn(n1.z - padR, W.ix, W.ox); t1 = __fmaf_rn(n2.y + padR, W.ix, W.ox);
+    float nearR = fminf(t0, t1), farR = fmaxf(t0, t1);
+    t0 = __fmaf_rn(n1.w - padR, W.iy, W.oy); t1 = __fmaf_rn(n2.z + padR, W.iy, W.oy);
+    nearR = fmaxf(nearR, fminf(t0, t1)); farR = fminf(farR, fmaxf(t0, t1));
+    t0 = __fmaf_rn(n2.x - padR, W.iz, W.oz); t1 = __fmaf_rn(n2.w + padR, W.iz, W.oz);
+    nearR = fmaxf(fmaxf(nearR, fminf(t0, t1)), 0.0f); farR = fminf(fminf(farR, fmaxf(t0, t1)), closest);
+    const bool hitL = nearL <= farL, hitR = nearR <= farR;
+    const int cL = __float_as_int(n3.x), cR = __float_as_int(n3.y);
+    if (hitL && hitR) {
+        const bool swap = nearR < nearL;  // descend into the nearer child, push the other
+        W.node = swap ? cR : cL;
+        stack[W.sp++] = make_int2(swap ? cL : cR, __float_as_int(swap ? nearL : nearR));
+    } else if (hitL) W.node = cL;
+    else if (hitR) W.node = cR;
+    else W.node = walk_pop(W, stack, closest);
+}
+
+// One leaf: test its primitive, pop.
+__device__ __forceinline__ void walk_leaf(const SceneView& S, const float4* __restrict__ sph,
+                                          const float4* __restrict__ tri, float3 o, float3 d, float a, Walk& W,
+                                          int2* stack, HitState& h, Winner& w) {
+    const int p = S.bvh_prim[~W.node];
+    if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w);
+    else try_triangle(S, tri, p - S.n_spheres, o, d, h, w);
+    W.node = walk_pop(W, stack, h.closest);
+}
+
+// One "while-while" step: internal nodes until a leaf is the current node, that leaf, pop.
+// Returns false once the walk is complete.
+__device__ __forceinline__ bool walk_step(const SceneView& S, const float4* __restrict__ sph,
+                                          const float4* __restrict__ tri, float3 o, float3 d, float a, Walk& W,
+                                          int2* stack, HitState& h, Winner& w) {
+    while (W.node >= 0) walk_inner(S, W, stack, h.closest);
+    if (W.node != kWalkDone) walk_leaf(S, sph, tri, o, d, a, W, stack, h, w);
+    return W.node != kWalkDone;
+}
+
 // MODE selects what a kernel instantiation carries: the brute-force scan with the primitives staged
 // in shared memory, the same scan reading them through L1/L2, or the LBVH walk (plus the linear scan
 // of the few "big" primitives the tree leaves out).  The scan kernels contain no tree code at all.
@@ -267,15 +403,7 @@ __device__ __forceinline__ void closest_hit(const SceneView& S, const float4* __
     h.t = 0.0f; h.p = f3(0.0f, 0.0f, 0.0f); h.n = f3(0.0f, 0.0f, 0.0f);
     h.closest = FLT_MAX; h.obj = -1;
     const float a = dot(d, d);  // sphere.rs:25
-    // Conservative whole-scene cull: the line o + t d stays farther than R from the centre C of the
-    // bounding sphere of every finite sphere and triangle iff a (|oc|^2 - R^2) - (oc.d)^2 > 0.  The
-    // margin 2^-16 a (|oc|^2 + R^2) exceeds the rounding error of this expression (<= 2^-20 of the same
-    // magnitude) plus the largest miss distance at which sphere.rs:25-29's disc or the triangle test
-    // can still accept (same order), so nothing the scan would accept is skipped.  NaN / inf inputs
-    // make the comparison false -> full scan.
-    const float3 occ = o - f3(S.cull_center);
-    const float ccc = dot(occ, occ), bcc = dot(occ, d);
-    const bool culled = a * (ccc - S.cull_r2) - bcc * bcc > 1.52587890625e-05f * (a * (ccc + S.cull_r2));
+    const bool culled = scene_culled(S, o, d, a);
     for (int sg = 0; sg < S.n_segments; ++sg) {
         Segment g = S.seg0;  // the first (usually only) segment travels in the constant bank
         if (sg > 0) g = S.segments[sg];
@@ -294,37 +422,8 @@ __device__ __forceinline__ void closest_hit(const SceneView& S, const float4* __
                 if (tree) bvh_closest(S, sph, tri, o, d, a, h, w);
             }
         }
-        if (w.kind >= 0) {  // what the last accepting hit() left in the shared HitRecord
-            h.t = h.closest;
-            h.p = o + h.t * d;  // ray.rs:30-32
-            if (w.kind == 0) {
-                const float4 s = sph[w.slot];
-                h.n = (h.p - xyz(s)) / s.w;  // sphere.rs:35,44
-            } else {
-                float3 n = f3(tri[3 * w.slot].w, tri[3 * w.slot + 1].w, tri[3 * w.slot + 2].w);
-                if (dot(d, n) > 0.0f) n = n * -1.0f;
-                h.n = n;
-            }
-            h.obj = w.obj;
-        }
-        if (g.plane >= 0) {  // plane.rs:24-44 (Q4: range test on denom; Q5: t, p written before the extent test)
-            const float3 position = xyz(S.planes[3 * g.plane]);
-            const float3 orientation = xyz(S.planes[3 * g.plane + 1]);
-            const float3 size = xyz(S.planes[3 * g.plane + 2]);
-            float denom = dot(orientation, d);
-            if (denom > kTMin && denom < h.closest) {
-                float3 plane_to_ray = position - o;
-                h.t = dot(plane_to_ray, orientation) / denom;
-                h.p = o + h.t * d;
-                if (h.p.x > position.x - size.x && h.p.x < position.x + size.x &&
-                    h.p.y > position.y - size.y && h.p.y < position.y + size.y &&
-                    h.p.z > position.z - size.z && h.p.z < position.z + size.z) {
-                    h.n = orientation * -1.0f;
-                    h.closest = h.t;  // tracer.rs:197
-                    h.obj = S.plane_obj[g.plane];
-                }
-            }
-        }
+        finalize_winner(sph, tri, o, d, w, h);
+        if (g.plane >= 0) plane_hit(S, g.plane, o, d, h);
     }
 }
 
