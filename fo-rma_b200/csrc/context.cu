@@ -73,7 +73,7 @@ struct forma_rt {
     // render_tree_kernel tuning (FORMA_RT_REFILL / FORMA_RT_LEAF_BATCH / FORMA_RT_WALK_MODE override; not part of the ABI)
     uint32_t refill = 16;     // lanes idle before a warp stops walking to refill them
     uint32_t leaf_batch = 8;  // walk_mode 1: lanes waiting at a leaf before the warp runs the primitive tests
-    uint32_t walk_mode = 0;   // 0: while-while steps, 1: one node per iteration with batched leaves
+    int walk_mode = -1;       // -1: by tree size; 0: while-while steps, 1: one node per iteration with batched leaves, 2: parked leaves
     uint32_t frame = 0;  // update() call counter -> sample index of the interactive frame
 
     // packed scene (host copies kept for re-upload after set_object)
@@ -402,7 +402,7 @@ int forma_rt_create(const forma_rt_options* opts, uint32_t width, uint32_t heigh
     }
     if (const char* r = std::getenv("FORMA_RT_WALK_MODE")) {
         const int v = std::atoi(r);
-        if (v == 0 || v == 1) c->walk_mode = (uint32_t)v;
+        if (v >= 0 && v <= 2) c->walk_mode = v;
     }
     // Scene::new (scene.rs:10-15): Camera::new + get_simple_scene
     c->scene.camera = forma::Camera::create(width, height);
@@ -557,7 +557,10 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
         CU_TRY(c->d_job.ensure(1));
         P.rad = c->d_rad.p; P.acc = c->d_acc.p; P.job_counter = c->d_job.p;
         P.rad_chunk = (uint32_t)chunk;
-        P.refill = c->refill; P.leaf_batch = c->leaf_batch; P.walk_mode = c->walk_mode;
+        P.refill = c->refill; P.leaf_batch = c->leaf_batch;
+        // measured (profiles/r01k_sweep.txt): deep trees spend their time at internal nodes and want the
+        // convergent one-node-per-iteration walk; shallow ones are leaf-heavy and want while-while steps
+        P.walk_mode = c->walk_mode >= 0 ? (uint32_t)c->walk_mode : (c->stats.bvh_nodes >= 4096u ? 1u : 0u);
     }
     uint32_t launches = 0;
     CU_TRY(cudaMemsetAsync(c->d_rays, 0, sizeof(unsigned long long), stream));

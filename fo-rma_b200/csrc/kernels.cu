@@ -137,9 +137,10 @@ __global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ 
 // Tree-mode path tracer (persistent warps).  Two things make a pixel-per-thread loop slow on scenes
 // with real bounces: rays of one warp need very different numbers of LBVH nodes, and pixels of one
 // tile need very different numbers of rays (sky next to a cluster of spheres).  So here
-//  * the (pixel, sample) pairs of a chunk of samples are JOBS in one global queue; a lane draws its
-//    next job when its path ends, so no lane idles while work is left anywhere on the GPU.  Jobs
-//    are ordered 8x4-pixel tile -> sample -> pixel, so a warp's primary rays stay coherent;
+//  * the (pixel, sample) pairs of a chunk of samples are JOBS.  A warp draws them in batches (8
+//    samples of one 8x4-pixel tile) from one global queue and hands them to its lanes as their
+//    paths end, so no lane idles while its warp has work and no warp idles while work is left
+//    anywhere on the GPU, yet the rays of a warp stay inside one or two tiles;
 //  * a finished path writes its radiance to rad[sample in chunk][pixel]; accumulate_kernel then
 //    adds every pixel's samples IN SAMPLE ORDER - the same f32 chain as tracer.rs:170-175, so the
 //    sums stay bit-identical to the flat loop and to the CPU restatement.  Cost: 32 B of HBM traffic per
@@ -152,6 +153,7 @@ __global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ 
 //    The warp walks until `refill` lanes have finished their walk (or none is walking), then those
 //    lanes shade, scatter or draw their next job and rejoin.
 enum : int { kNewPath = 0, kStart = 1, kWalk = 2, kShade = 3 };
+constexpr int kBatchSamples = 8;
 
 __global__ void __launch_bounds__(kBlock) render_tree_kernel(const __grid_constant__ RenderParams P) {
     const SceneView& S = P.scene;
@@ -159,13 +161,17 @@ __global__ void __launch_bounds__(kBlock) render_tree_kernel(const __grid_consta
     const int lane = threadIdx.x & 31;
     constexpr unsigned kFull = 0xffffffffu;
     const uint32_t tiles_x = (P.width + 7) / 8, tiles_y = (P.height + 3) / 4;
-    const uint32_t n_jobs = tiles_x * tiles_y * P.chunk_k * 32u;  // < 2^32: checked by the launcher
+    const uint32_t groups = (P.chunk_k + kBatchSamples - 1) / kBatchSamples;
+    const uint32_t n_batches = tiles_x * tiles_y * groups;  // < 2^32: checked by the launcher
+    uint32_t batch_next = 0, batch_jobs = 0, batch_x = 0, batch_y = 0, batch_k0 = 0;  // warp-uniform
     const float fw = (float)P.width, fh = (float)P.height;
     const bool no_jitter = P.flags & FORMA_RT_NO_JITTER, pinhole = P.flags & FORMA_RT_PINHOLE;
 
     uint32_t rays = 0;
     int astack[kMaxDepthCap];   // list indices of the hit objects: attenuations multiply innermost first
-    int2 wstack[64];            // walk stack: (child, entry distance)
+    __shared__ int2 stack_smem[kSmemStack * kWalkBlock];
+    int2 stack_local[kStackCap - kSmemStack];
+    const WalkStack wstack{stack_smem + threadIdx.x, stack_local};
     PathRng rng{P.rk, 0u, 0u};
     uint32_t depth = 0, slot = 0;  // slot: where this path's radiance goes in `rad`
     int phase = kNewPath;
@@ -176,7 +182,7 @@ __global__ void __launch_bounds__(kBlock) render_tree_kernel(const __grid_consta
     Winner w;
     Walk W;
     h.t = 0.0f; h.p = o; h.n = o; h.closest = FLT_MAX; h.obj = -1;
-    W.ix = W.iy = W.iz = W.ox = W.oy = W.oz = W.coef = 0.0f; W.node = kWalkDone; W.sp = 0;
+    W.ix = W.iy = W.iz = W.ox = W.oy = W.oz = W.coef = 0.0f; W.node = kWalkDone; W.sp = 0; W.leaf = kWalkDone;
 
     for (;;) {
         // ---- A. shade the rays whose walk has finished
@@ -209,27 +215,30 @@ __global__ void __launch_bounds__(kBlock) render_tree_kernel(const __grid_consta
                 phase = kNewPath;
             }
         }
-        // ---- B. one queue transaction for all lanes of the warp that need a job
-        const unsigned need = __ballot_sync(kFull, phase == kNewPath && !lane_done);
-        if (need != 0u) {
-            unsigned base = 0;
-            if (lane == __ffs(need) - 1) base = atomicAdd(P.job_counter, (unsigned)__popc(need));
-            base = __shfl_sync(kFull, base, __ffs(need) - 1);
-            if (phase == kNewPath && !lane_done) {
+        // ---- B. hand the warp's next jobs to the lanes that need one.  The warp owns one BATCH at a time:
+        // kBatchSamples consecutive samples of one 8x4 tile, job j = (sample j >> 5, pixel j & 31), so
+        // a refilled lane stays inside the tile its neighbours are tracing; one atomic per batch.
+        for (;;) {
+            const bool want = phase == kNewPath && !lane_done;
+            const unsigned need = __ballot_sync(kFull, want);
+            if (need == 0u) break;
+            if (batch_next >= batch_jobs) {  // warp-uniform: draw the next batch
+                unsigned b = 0;
+                if (lane == 0) b = atomicAdd(P.job_counter, 1u);
+                b = __shfl_sync(kFull, b, 0);
+                if (b >= n_batches) { if (want) lane_done = true; break; }
+                const uint32_t tile = b / groups, grp = b % groups;
+                batch_x = (tile % tiles_x) * 8u; batch_y = (tile / tiles_x) * 4u;
+                batch_k0 = grp * kBatchSamples;
+                batch_jobs = min((uint32_t)kBatchSamples, P.chunk_k - batch_k0) * 32u;
+                batch_next = 0;
+            }
+            const uint32_t job = batch_next + __popc(need & ((1u << lane) - 1u));
+            batch_next = min(batch_next + (uint32_t)__popc(need), batch_jobs);
+            if (want && job < batch_jobs) {
                 // ---- C. decode the job, generate its camera ray
-                uint32_t job = base + __popc(need & ((1u << lane) - 1u));
-                uint32_t jx = 0, jy = 0, k = 0;
-                bool have = false;
-                while (job < n_jobs) {  // jobs of pixels outside the image (partial edge tiles) are skipped
-                    const uint32_t t = job & 31u, rest = job >> 5;
-                    k = rest % P.chunk_k;
-                    const uint32_t tile = rest / P.chunk_k;
-                    jx = (tile % tiles_x) * 8u + (t & 7u); jy = (tile / tiles_x) * 4u + (t >> 3);
-                    if (jx < P.width && jy < P.height) { have = true; break; }
-                    job = atomicAdd(P.job_counter, 1u);
-                }
-                if (!have) lane_done = true;
-                else {
+                const uint32_t jx = batch_x + (job & 7u), jy = batch_y + ((job >> 3) & 3u), k = batch_k0 + (job >> 5);
+                if (jx < P.width && jy < P.height) {  // jobs of pixels outside the image (edge tiles) are dropped
                     rng.pixel = jx + jy * P.width;
                     rng.sample = P.sample_offset + P.chunk_base + k;
                     slot = k * (P.width * P.height) + rng.pixel;
@@ -271,7 +280,7 @@ __global__ void __launch_bounds__(kBlock) render_tree_kernel(const __grid_consta
                 const unsigned idle = __ballot_sync(kFull, !lane_done && phase != kWalk);
                 if (walking == 0u || __popc(idle) >= (int)P.refill) break;
             }
-        } else {
+        } else if (P.walk_mode == 1u) {
             // one node per lane and iteration; lanes that reach a leaf wait there until `leaf_batch` of
             // them can test their primitives together (or no lane is at an internal node)
             for (;;) {
@@ -286,6 +295,34 @@ __global__ void __launch_bounds__(kBlock) render_tree_kernel(const __grid_consta
                 const unsigned walking = __ballot_sync(kFull, phase == kWalk);
                 const unsigned idle = __ballot_sync(kFull, !lane_done && phase != kWalk);
                 if (walking == 0u || __popc(idle) >= (int)P.refill) break;
+            }
+        } else {
+            // one node per lane and iteration.  A lane that arrives at a leaf PARKS it and walks on with
+            // the next stack entry; only with a second leaf (or an empty stack) does it wait.  When
+            // `leaf_batch` lanes wait (or no lane is at an internal node) every parked leaf of the warp
+            // is tested together.  Any visiting order gives the scan's result (Winner's tie rule).
+            for (;;) {
+                const bool walking = phase == kWalk;
+                if (walking && W.node >= 0) walk_inner(S, W, wstack, h.closest);
+                if (walking && W.node < 0 && W.node != kWalkDone && W.leaf == kWalkDone) {
+                    W.leaf = W.node;
+                    W.node = walk_pop(W, wstack, h.closest);
+                }
+                const bool waiting = walking && W.node < 0 && W.leaf != kWalkDone;
+                const unsigned nwait = __ballot_sync(kFull, waiting);
+                const unsigned inner = __ballot_sync(kFull, walking && W.node >= 0);
+                if (nwait != 0u && (__popc(nwait) >= (int)P.leaf_batch || inner == 0u)) {
+                    if (walking && W.leaf != kWalkDone) {
+                        const int p = S.bvh_prim[~W.leaf];
+                        if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w);
+                        else try_triangle(S, tri, p - S.n_spheres, o, d, h, w);
+                        W.leaf = kWalkDone;
+                    }
+                }
+                if (walking && W.node == kWalkDone && W.leaf == kWalkDone) phase = kShade;
+                const unsigned still = __ballot_sync(kFull, phase == kWalk);
+                const unsigned idle = __ballot_sync(kFull, !lane_done && phase != kWalk);
+                if (still == 0u || __popc(idle) >= (int)P.refill) break;
             }
         }
     }
@@ -397,7 +434,7 @@ static cudaError_t launch_render_tree(RenderParams P, int sm_count, cudaStream_t
     const size_t npix = (size_t)P.width * P.height;
     for (uint32_t base = 0; base < P.spp; base += P.rad_chunk) {
         uint32_t k = P.spp - base < P.rad_chunk ? P.spp - base : P.rad_chunk;
-        while (tiles * k * 32u >= (1ull << 32)) k = (k + 1) / 2;  // job indices are 32-bit
+        while (tiles * k >= (1ull << 32)) k = (k + 1) / 2;  // batch indices are 32-bit
         P.chunk_base = base; P.chunk_k = k;
         if ((e = cudaMemsetAsync(P.job_counter, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
         render_tree_kernel<<<grid, kBlock, 0, stream>>>(P);

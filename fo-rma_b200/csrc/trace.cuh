@@ -107,13 +107,18 @@ __device__ __forceinline__ void camera_ray(const forma_rt_camera& c, const PathR
     float3 offset = f3(0.0f, 0.0f, 0.0f);
     if (!pinhole) {
         float px = 2.0f * r0.z - 1.0f, py = 2.0f * r0.w - 1.0f;
-        // dot(p,p) with p.z = 2*0 - 0 = 0: (x*x + y*y) + 0*0
-        uint32_t blk = 0;
-        bool second_half = true;
-        Rand4 r = r0;
-        while ((px * px + py * py) + 0.0f >= 1.0f) {
-            if (second_half) { ++blk; r = rng.block(0, blk); second_half = false; px = 2.0f * r.x - 1.0f; py = 2.0f * r.y - 1.0f; }
-            else { second_half = true; px = 2.0f * r.z - 1.0f; py = 2.0f * r.w - 1.0f; }
+        // utility.rs:4-13: retry while dot(p,p) >= 1 with p.z = 0.  (x*x + y*y) + 0*0 == x*x + y*y: a sum
+        // of squares is never -0.  Both tries of a retry block are evaluated branch-free.
+        if (px * px + py * py >= 1.0f) {
+            uint32_t blk = 0;
+            for (;;) {
+                const Rand4 r = rng.block(0, ++blk);
+                px = 2.0f * r.x - 1.0f; py = 2.0f * r.y - 1.0f;
+                const float qx = 2.0f * r.z - 1.0f, qy = 2.0f * r.w - 1.0f;
+                const bool ok1 = !(px * px + py * py >= 1.0f), ok2 = !(qx * qx + qy * qy >= 1.0f);
+                if (!ok1) { px = qx; py = qy; }
+                if (ok1 || ok2) break;
+            }
         }
         float rdx = c.lens_radius * px, rdy = c.lens_radius * py;  // camera.rs:63
         offset = rdx * f3(c.u) + rdy * f3(c.v);                      // camera.rs:64
@@ -320,6 +325,7 @@ struct Walk {
     float coef;                    // 2^-19 (|o - C|^2 + R^2): the pad scale of this ray
     int node;                      // >= 0 internal, < 0 leaf ~node, kWalkDone
     int sp;
+    int leaf;                      // walk_mode 2: a leaf parked for the next batch of primitive tests, or kWalkDone
 };
 
 __device__ __forceinline__ void walk_begin(const SceneView& S, float3 o, float3 d, Walk& W) {
@@ -332,18 +338,33 @@ __device__ __forceinline__ void walk_begin(const SceneView& S, float3 o, float3 
     W.coef = 1.9073486e-6f * (dot(oc, oc) + S.bvh_r2);  // 2^-19
     W.node = 0;
     W.sp = 0;
+    W.leaf = kWalkDone;
 }
 
-__device__ __forceinline__ int walk_pop(Walk& W, const int2* stack, float closest) {
+// Walk stack: (child, entry distance) pairs.  The first kSmemStack levels of every thread live in
+// shared memory (level-major, one 8-byte word per thread: conflict-free), deeper levels in local
+// memory - so the hot part of the stacks no longer competes with the tree for L1.
+constexpr int kSmemStack = 16, kStackCap = 64, kWalkBlock = 128;
+struct WalkStack {
+    int2* smem;   // this thread's column: level l at smem[l * kWalkBlock]
+    int2* local;  // levels >= kSmemStack
+    __device__ __forceinline__ void push(int sp, int2 e) const {
+        if (sp < kSmemStack) smem[sp * kWalkBlock] = e;
+        else local[sp - kSmemStack] = e;
+    }
+    __device__ __forceinline__ int2 at(int sp) const { return sp < kSmemStack ? smem[sp * kWalkBlock] : local[sp - kSmemStack]; }
+};
+
+__device__ __forceinline__ int walk_pop(Walk& W, const WalkStack& stack, float closest) {
     while (W.sp > 0) {
-        const int2 e = stack[--W.sp];
+        const int2 e = stack.at(--W.sp);
         if (__int_as_float(e.y) <= closest) return e.x;  // <=: an equal t with a smaller list index still wins
     }
     return kWalkDone;
 }
 
 // One internal node: test both child boxes, descend into the nearer hit child (pushing the other) or pop.
-__device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, int2* stack, float closest) {
+__device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, const WalkStack& stack, float closest) {
     const int node = W.node;
     const float eps = S.bvh_eps;
     const float4 n0 = __ldg(S.bvh_nodes + 4 * node), n1 = __ldg(S.bvh_nodes + 4 * node + 1);
@@ -366,7 +387,7 @@ __device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, int2* st
     if (hitL && hitR) {
         const bool swap = nearR < nearL;  // descend into the nearer child, push the other
         W.node = swap ? cR : cL;
-        stack[W.sp++] = make_int2(swap ? cL : cR, __float_as_int(swap ? nearL : nearR));
+        stack.push(W.sp++, make_int2(swap ? cL : cR, __float_as_int(swap ? nearL : nearR)));
     } else if (hitL) W.node = cL;
     else if (hitR) W.node = cR;
     else W.node = walk_pop(W, stack, closest);
@@ -375,7 +396,7 @@ __device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, int2* st
 // One leaf: test its primitive, pop.
 __device__ __forceinline__ void walk_leaf(const SceneView& S, const float4* __restrict__ sph,
                                           const float4* __restrict__ tri, float3 o, float3 d, float a, Walk& W,
-                                          int2* stack, HitState& h, Winner& w) {
+                                          const WalkStack& stack, HitState& h, Winner& w) {
     const int p = S.bvh_prim[~W.node];
     if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w);
     else try_triangle(S, tri, p - S.n_spheres, o, d, h, w);
@@ -386,7 +407,7 @@ __device__ __forceinline__ void walk_leaf(const SceneView& S, const float4* __re
 // Returns false once the walk is complete.
 __device__ __forceinline__ bool walk_step(const SceneView& S, const float4* __restrict__ sph,
                                           const float4* __restrict__ tri, float3 o, float3 d, float a, Walk& W,
-                                          int2* stack, HitState& h, Winner& w) {
+                                          const WalkStack& stack, HitState& h, Winner& w) {
     while (W.node >= 0) walk_inner(S, W, stack, h.closest);
     if (W.node != kWalkDone) walk_leaf(S, sph, tri, o, d, a, W, stack, h, w);
     return W.node != kWalkDone;
