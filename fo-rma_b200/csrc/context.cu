@@ -72,8 +72,8 @@ struct forma_rt {
     bool stats_pending = false;
     // render_tree_kernel tuning (FORMA_RT_REFILL / FORMA_RT_LEAF_BATCH / FORMA_RT_WALK_MODE override; not part of the ABI)
     uint32_t refill = 16;     // lanes idle before a warp stops walking to refill them
-    uint32_t leaf_batch = 8;  // walk_mode 1: lanes waiting at a leaf before the warp runs the primitive tests
-    int walk_mode = -1;       // -1: by tree size; 0: while-while steps, 1: one node per iteration with batched leaves, 2: parked leaves
+    uint32_t leaf_batch = 8;  // walk_mode 1: lanes that must stop progressing before the warp looks at its waiting leaves
+    int walk_mode = -1;       // -1: by tree size; 0: while-while steps, 1: convergent walk (one node per lane and iteration)
     uint32_t frame = 0;  // update() call counter -> sample index of the interactive frame
 
     // packed scene (host copies kept for re-upload after set_object)
@@ -402,7 +402,7 @@ int forma_rt_create(const forma_rt_options* opts, uint32_t width, uint32_t heigh
     }
     if (const char* r = std::getenv("FORMA_RT_WALK_MODE")) {
         const int v = std::atoi(r);
-        if (v >= 0 && v <= 2) c->walk_mode = v;
+        if (v >= 0 && v <= 1) c->walk_mode = v;
     }
     // Scene::new (scene.rs:10-15): Camera::new + get_simple_scene
     c->scene.camera = forma::Camera::create(width, height);

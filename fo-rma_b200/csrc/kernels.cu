@@ -60,8 +60,11 @@ __device__ __forceinline__ void write_out(const RenderParams& P, float3 col, uin
     }
 }
 
+#ifndef FORMA_SCAN_MIN_BLOCKS
+#define FORMA_SCAN_MIN_BLOCKS 6
+#endif
 template <int MODE>
-__global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ RenderParams P) {
+__global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(const __grid_constant__ RenderParams P) {
     const float4 *sph, *tri;
     stage_scene<MODE>(P.scene, sph, tri);
 
@@ -155,7 +158,10 @@ __global__ void __launch_bounds__(kBlock) render_kernel(const __grid_constant__ 
 enum : int { kNewPath = 0, kStart = 1, kWalk = 2, kShade = 3 };
 constexpr int kBatchSamples = 8;
 
-__global__ void __launch_bounds__(kBlock) render_tree_kernel(const __grid_constant__ RenderParams P) {
+#ifndef FORMA_TREE_MIN_BLOCKS
+#define FORMA_TREE_MIN_BLOCKS 8  // 64 registers: 32 resident warps / SM (profiles/r01p_occ.txt: A 134 -> 122 ms, D 142 -> 138 ms)
+#endif
+__global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_kernel(const __grid_constant__ RenderParams P) {
     const SceneView& S = P.scene;
     const float4 *sph = S.spheres, *tri = S.tris;
     const int lane = threadIdx.x & 31;
@@ -182,7 +188,7 @@ __global__ void __launch_bounds__(kBlock) render_tree_kernel(const __grid_consta
     Winner w;
     Walk W;
     h.t = 0.0f; h.p = o; h.n = o; h.closest = FLT_MAX; h.obj = -1;
-    W.ix = W.iy = W.iz = W.ox = W.oy = W.oz = W.coef = 0.0f; W.node = kWalkDone; W.sp = 0; W.leaf = kWalkDone;
+    W.ix = W.iy = W.iz = W.ox = W.oy = W.oz = W.coef = 0.0f; W.node = kWalkDone; W.sp = 0;
 
     for (;;) {
         // ---- A. shade the rays whose walk has finished
@@ -280,49 +286,39 @@ __global__ void __launch_bounds__(kBlock) render_tree_kernel(const __grid_consta
                 const unsigned idle = __ballot_sync(kFull, !lane_done && phase != kWalk);
                 if (walking == 0u || __popc(idle) >= (int)P.refill) break;
             }
-        } else if (P.walk_mode == 1u) {
-            // one node per lane and iteration; lanes that reach a leaf wait there until `leaf_batch` of
-            // them can test their primitives together (or no lane is at an internal node)
-            for (;;) {
-                if (phase == kWalk && W.node >= 0) walk_inner(S, W, wstack, h.closest);
-                const bool at_leaf = phase == kWalk && W.node < 0 && W.node != kWalkDone;
-                const unsigned leaves = __ballot_sync(kFull, at_leaf);
-                const unsigned inner = __ballot_sync(kFull, phase == kWalk && W.node >= 0);
-                if (leaves != 0u && (__popc(leaves) >= (int)P.leaf_batch || inner == 0u)) {
-                    if (at_leaf) walk_leaf(S, sph, tri, o, d, a, W, wstack, h, w);
-                }
-                if (phase == kWalk && W.node == kWalkDone) phase = kShade;
-                const unsigned walking = __ballot_sync(kFull, phase == kWalk);
-                const unsigned idle = __ballot_sync(kFull, !lane_done && phase != kWalk);
-                if (walking == 0u || __popc(idle) >= (int)P.refill) break;
-            }
         } else {
-            // one node per lane and iteration.  A lane that arrives at a leaf PARKS it and walks on with
-            // the next stack entry; only with a second leaf (or an empty stack) does it wait.  When
-            // `leaf_batch` lanes wait (or no lane is at an internal node) every parked leaf of the warp
-            // is tested together.  Any visiting order gives the scan's result (Winner's tie rule).
+            // Convergent walk: per iteration every walking lane takes ONE stack entry (if it needs one)
+            // and tests ONE internal node, so lanes never wait for each other inside a node or a pop
+            // loop.  Lanes that reach a leaf, finish or idle stop progressing; the warp looks at them only
+            // once `leaf_batch` more lanes have stopped (one ballot per iteration until then), tests the
+            // waiting leaves together, and leaves the loop when `refill` lanes are ready to shade.
+            // Any visiting order gives the scan's result (Winner's tie rule).
+            int wake_at = 0;
             for (;;) {
                 const bool walking = phase == kWalk;
-                if (walking && W.node >= 0) walk_inner(S, W, wstack, h.closest);
-                if (walking && W.node < 0 && W.node != kWalkDone && W.leaf == kWalkDone) {
-                    W.leaf = W.node;
-                    W.node = walk_pop(W, wstack, h.closest);
-                }
-                const bool waiting = walking && W.node < 0 && W.leaf != kWalkDone;
-                const unsigned nwait = __ballot_sync(kFull, waiting);
-                const unsigned inner = __ballot_sync(kFull, walking && W.node >= 0);
-                if (nwait != 0u && (__popc(nwait) >= (int)P.leaf_batch || inner == 0u)) {
-                    if (walking && W.leaf != kWalkDone) {
-                        const int p = S.bvh_prim[~W.leaf];
-                        if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w);
-                        else try_triangle(S, tri, p - S.n_spheres, o, d, h, w);
-                        W.leaf = kWalkDone;
+                if (walking && W.node == kWalkPop) {
+                    if (W.sp == 0) W.node = kWalkDone;
+                    else {
+                        const int2 e = wstack.at(--W.sp);
+                        if (__int_as_float(e.y) <= h.closest) W.node = e.x;  // else: stays kWalkPop
                     }
                 }
-                if (walking && W.node == kWalkDone && W.leaf == kWalkDone) phase = kShade;
-                const unsigned still = __ballot_sync(kFull, phase == kWalk);
-                const unsigned idle = __ballot_sync(kFull, !lane_done && phase != kWalk);
-                if (still == 0u || __popc(idle) >= (int)P.refill) break;
+                if (walking && W.node >= 0) walk_inner<true>(S, W, wstack, h.closest);
+                const bool busy = walking && (W.node >= 0 || W.node == kWalkPop);
+                const int stopped = 32 - __popc(__ballot_sync(kFull, busy));
+                if (stopped < wake_at) continue;
+                if (walking && W.node == kWalkDone) phase = kShade;
+                const bool at_leaf = phase == kWalk && !busy;
+                const unsigned leaves = __ballot_sync(kFull, at_leaf);
+                const int idle = __popc(__ballot_sync(kFull, !lane_done && phase != kWalk));
+                if (idle >= (int)P.refill || (stopped == 32 && leaves == 0u)) break;
+                if (at_leaf) {
+                    const int p = ~W.node;
+                    if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w);
+                    else try_triangle(S, tri, p - S.n_spheres, o, d, h, w);
+                    W.node = kWalkPop;
+                }
+                wake_at = min(32, stopped - __popc(leaves) + (int)P.leaf_batch);
             }
         }
     }

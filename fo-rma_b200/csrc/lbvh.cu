@@ -7,10 +7,10 @@
 //   [4k+0] = (Lmin.x, Lmin.y, Lmin.z, Lmax.x)
 //   [4k+1] = (Lmax.y, Lmax.z, Rmin.x, Rmin.y)
 //   [4k+2] = (Rmin.z, Rmax.x, Rmax.y, Rmax.z)
-//   [4k+3] = (bits(L), bits(R), qL, qR)   child >= 0: internal node; child < 0: leaf ~child
+//   [4k+3] = (bits(L), bits(R), qL, qR)   child >= 0: internal node; child < 0: ~(unified primitive index)
 // q = max over the child's subtree of 1/radius (0 for triangles): the walk pads a box by
 // coef(ray) * q + eps so that the f32 sphere test of sphere.rs:23-51 can never report a hit that the
-// box test culled (DESIGN.md "LBVH").  Leaf l holds primitive prim[l] (sorted order).
+// box test culled (DESIGN.md "LBVH").  prim[l] = primitive of sorted leaf l is kept for tooling only.
 #include <cfloat>
 #include <cstdint>
 
@@ -118,7 +118,11 @@ __device__ __forceinline__ Box child_box(int c, const float4* __restrict__ leaf_
 
 // Bottom-up: each leaf climbs; the second thread to reach a node (atomic flag) sees both children
 // complete, writes the node record and the node's own box, and continues upward.
-__global__ void refit_kernel(int n, const int2* __restrict__ children, const int* __restrict__ parent,
+__device__ __forceinline__ int leaf_to_prim(const LbvhInput& in, int i) {  // leaf id (pre-sort) -> unified primitive index
+    return i < in.n_bvh_spheres ? in.big_spheres + i : in.n_spheres + in.big_tris + (i - in.n_bvh_spheres);
+}
+
+__global__ void refit_kernel(LbvhInput in, int n, const int2* __restrict__ children, const int* __restrict__ parent,
                              const float4* __restrict__ leaf_lo, const float4* __restrict__ leaf_hi,
                              const int* __restrict__ sorted_leaf, float4* node_lo, float4* node_hi,
                              unsigned int* __restrict__ flags, float4* __restrict__ nodes) {
@@ -135,7 +139,9 @@ __global__ void refit_kernel(int n, const int2* __restrict__ children, const int
         nodes[4 * node + 0] = make_float4(L.lo.x, L.lo.y, L.lo.z, L.hi.x);
         nodes[4 * node + 1] = make_float4(L.hi.y, L.hi.z, R.lo.x, R.lo.y);
         nodes[4 * node + 2] = make_float4(R.lo.z, R.hi.x, R.hi.y, R.hi.z);
-        nodes[4 * node + 3] = make_float4(__int_as_float(ch.x), __int_as_float(ch.y), L.q, R.q);
+        const int cl = ch.x < 0 ? ~leaf_to_prim(in, sorted_leaf[~ch.x]) : ch.x;
+        const int cr = ch.y < 0 ? ~leaf_to_prim(in, sorted_leaf[~ch.y]) : ch.y;
+        nodes[4 * node + 3] = make_float4(__int_as_float(cl), __int_as_float(cr), L.q, R.q);
         __stcg(node_lo + node, make_float4(fminf(L.lo.x, R.lo.x), fminf(L.lo.y, R.lo.y), fminf(L.lo.z, R.lo.z), fmaxf(L.q, R.q)));
         __stcg(node_hi + node, make_float4(fmaxf(L.hi.x, R.hi.x), fmaxf(L.hi.y, R.hi.y), fmaxf(L.hi.z, R.hi.z), 0.0f));
         node = parent[node];
@@ -147,7 +153,7 @@ __global__ void leaf_prim_kernel(LbvhInput in, const int* __restrict__ sorted_le
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
     if (l >= in.count) return;
     const int i = sorted_leaf[l];
-    prim[l] = i < in.n_bvh_spheres ? in.big_spheres + i : in.n_spheres + in.big_tris + (i - in.n_bvh_spheres);
+    prim[l] = leaf_to_prim(in, i);
 }
 
 }  // namespace
@@ -205,7 +211,7 @@ cudaError_t LbvhDevice::build(const LbvhInput& in, cudaStream_t stream) {
     hierarchy_kernel<<<G, B, 0, stream>>>(sorted_keys, n, children, parent);
     LB_TRY(cudaGetLastError());
     LB_TRY(cudaMemsetAsync(flags, 0, sizeof(unsigned int) * (n - 1), stream));
-    refit_kernel<<<G, B, 0, stream>>>(n, children, parent, leaf_lo, leaf_hi, sorted_leaf, node_lo, node_hi, flags, nodes);
+    refit_kernel<<<G, B, 0, stream>>>(in, n, children, parent, leaf_lo, leaf_hi, sorted_leaf, node_lo, node_hi, flags, nodes);
     LB_TRY(cudaGetLastError());
     leaf_prim_kernel<<<G, B, 0, stream>>>(in, sorted_leaf, prim);
     LB_TRY(cudaGetLastError());

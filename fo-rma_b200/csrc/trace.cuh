@@ -250,6 +250,17 @@ __device__ __forceinline__ bool scene_culled(const SceneView& S, float3 o, float
     return a * (cc - S.cull_r2) - b * b > 1.52587890625e-05f * (a * (cc + S.cull_r2));
 }
 
+// One 64-byte node record as two 256-bit loads (LDG.E.256, sm_100+): a warp's lanes sit at different
+// nodes, so every load instruction costs one L1 tag look-up per lane - two per node instead of four.
+__device__ __forceinline__ void load_node(const float4* __restrict__ nodes, int node, float4& n0, float4& n1,
+                                          float4& n2, float4& n3) {
+    const float4* p = nodes + 4 * (size_t)node;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(n0.x), "=f"(n0.y), "=f"(n0.z), "=f"(n0.w), "=f"(n1.x), "=f"(n1.y), "=f"(n1.z), "=f"(n1.w) : "l"(p));
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(n2.x), "=f"(n2.y), "=f"(n2.z), "=f"(n2.w), "=f"(n3.x), "=f"(n3.y), "=f"(n3.z), "=f"(n3.w) : "l"(p + 2));
+}
+
 // LBVH walk over the primitives the tree indexes (lbvh.cu).  Exactness: a child box is visited iff
 // the ray's interval through the PADDED box reaches [0, closest]; the pad
 //     coef(ray) * q(child) + eps,   coef = 2^-19 (|o - C|^2 + R^2),  q = max 1/r below the child
@@ -273,8 +284,8 @@ __device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __
     int sp = 0;
     int node = 0;
     for (;;) {
-        const float4 n0 = __ldg(S.bvh_nodes + 4 * node), n1 = __ldg(S.bvh_nodes + 4 * node + 1);
-        const float4 n2 = __ldg(S.bvh_nodes + 4 * node + 2), n3 = __ldg(S.bvh_nodes + 4 * node + 3);
+        float4 n0, n1, n2, n3;
+        load_node(S.bvh_nodes, node, n0, n1, n2, n3);
         const float padL = __fmaf_rn(coef, n3.z, eps), padR = __fmaf_rn(coef, n3.w, eps);
         // slab test, (b - o) / d as fma(b, 1/d, -o/d); explicit fma: this part need not match the oracle
         float t0 = __fmaf_rn(n0.x - padL, ix, ox), t1 = __fmaf_rn(n0.w + padL, ix, ox);
@@ -296,14 +307,14 @@ __device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __
         if (hitL && hitR) {
             if (nearR < nearL) { const int t = cL; cL = cR; cR = t; }  // cL = nearer child
             // leaves are tested on the spot, internal nodes are descended / pushed
-            if (cL < 0) { const int p = S.bvh_prim[~cL]; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
+            if (cL < 0) { const int p = ~cL; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
             else { next = cL; have = true; }
-            if (cR < 0) { const int p = S.bvh_prim[~cR]; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
+            if (cR < 0) { const int p = ~cR; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
             else if (have) { stack[sp++] = cR; }
             else { next = cR; have = true; }
         } else if (hitL || hitR) {
             const int c = hitL ? cL : cR;
-            if (c < 0) { const int p = S.bvh_prim[~c]; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
+            if (c < 0) { const int p = ~c; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
             else { next = c; have = true; }
         }
         if (have) { node = next; continue; }
@@ -318,14 +329,14 @@ __device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __
 // traversal with ray regeneration).  One step = descend through internal nodes until a leaf is the
 // current node, test that leaf's primitive, pop.  Stack entries carry the entry distance of the
 // pushed child so a pop skips subtrees that the hits found meanwhile have put out of range.
-constexpr int kWalkDone = (int)0x80000000;  // never a leaf code: leaves are ~l with l < 2^31 - 1
+constexpr int kWalkDone = (int)0x80000000;  // never a leaf code: leaves are ~l with l < 2^31 - 2
+constexpr int kWalkPop = (int)0x80000001;   // convergent walk: this lane takes its next node from the stack
 
 struct Walk {
     float ix, iy, iz, ox, oy, oz;  // 1/d and -o/d
     float coef;                    // 2^-19 (|o - C|^2 + R^2): the pad scale of this ray
     int node;                      // >= 0 internal, < 0 leaf ~node, kWalkDone
     int sp;
-    int leaf;                      // walk_mode 2: a leaf parked for the next batch of primitive tests, or kWalkDone
 };
 
 __device__ __forceinline__ void walk_begin(const SceneView& S, float3 o, float3 d, Walk& W) {
@@ -338,7 +349,6 @@ __device__ __forceinline__ void walk_begin(const SceneView& S, float3 o, float3 
     W.coef = 1.9073486e-6f * (dot(oc, oc) + S.bvh_r2);  // 2^-19
     W.node = 0;
     W.sp = 0;
-    W.leaf = kWalkDone;
 }
 
 // Walk stack: (child, entry distance) pairs.  The first kSmemStack levels of every thread live in
@@ -363,12 +373,14 @@ __device__ __forceinline__ int walk_pop(Walk& W, const WalkStack& stack, float c
     return kWalkDone;
 }
 
-// One internal node: test both child boxes, descend into the nearer hit child (pushing the other) or pop.
+// One internal node: test both child boxes, descend into the nearer hit child (pushing the other) or pop
+// (LAZY_POP: leave the pop to the caller's next iteration).
+template <bool LAZY_POP = false>
 __device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, const WalkStack& stack, float closest) {
     const int node = W.node;
     const float eps = S.bvh_eps;
-    const float4 n0 = __ldg(S.bvh_nodes + 4 * node), n1 = __ldg(S.bvh_nodes + 4 * node + 1);
-    const float4 n2 = __ldg(S.bvh_nodes + 4 * node + 2), n3 = __ldg(S.bvh_nodes + 4 * node + 3);
+    float4 n0, n1, n2, n3;
+    load_node(S.bvh_nodes, node, n0, n1, n2, n3);
     const float padL = __fmaf_rn(W.coef, n3.z, eps), padR = __fmaf_rn(W.coef, n3.w, eps);
     float t0 = __fmaf_rn(n0.x - padL, W.ix, W.ox), t1 = __fmaf_rn(n0.w + padL, W.ix, W.ox);
     float nearL = fminf(t0, t1), farL = fmaxf(t0, t1);
@@ -390,14 +402,14 @@ __device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, const Wa
         stack.push(W.sp++, make_int2(swap ? cL : cR, __float_as_int(swap ? nearL : nearR)));
     } else if (hitL) W.node = cL;
     else if (hitR) W.node = cR;
-    else W.node = walk_pop(W, stack, closest);
+    else W.node = LAZY_POP ? kWalkPop : walk_pop(W, stack, closest);
 }
 
 // One leaf: test its primitive, pop.
 __device__ __forceinline__ void walk_leaf(const SceneView& S, const float4* __restrict__ sph,
                                           const float4* __restrict__ tri, float3 o, float3 d, float a, Walk& W,
                                           const WalkStack& stack, HitState& h, Winner& w) {
-    const int p = S.bvh_prim[~W.node];
+    const int p = ~W.node;  // leaf codes are the complemented unified primitive index
     if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w);
     else try_triangle(S, tri, p - S.n_spheres, o, d, h, w);
     W.node = walk_pop(W, stack, h.closest);

@@ -23,7 +23,8 @@ rows = list(csv.reader(io.StringIO(out)))
 hdr = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
 ci = {k: i for i, k in enumerate(rows[hdr])}
 base = None
-ops, opst, lines, linest = (collections.Counter() for _ in range(4))
+ops, opst, lines, linest, stall = (collections.Counter() for _ in range(5))
+ts = 0
 tw = tt = 0
 for r in rows[hdr + 1:]:
     try:
@@ -35,6 +36,9 @@ for r in rows[hdr + 1:]:
     op = next((x for x in r[ci["Source"]].split() if not x.startswith("@")), "?").split(".")[0]
     ops[op] += w; opst[op] += t
     k = line_of.get(addr - base, ("?", 0)); lines[k] += w; linest[k] += t
+    try: sm = int(r[ci["Warp Stall Sampling (All Samples)"]])
+    except (ValueError, KeyError): sm = 0
+    stall[k] += sm; ts += sm
 print(f"warp instr {tw:.4g}  thread instr {tt:.4g}  avg active {tt / max(tw, 1):.2f}")
 for op, w in ops.most_common(top // 2):
     print(f"{op:10s} {w:14d} {100 * w / tw:6.2f}%  active {opst[op] / max(w, 1):5.1f}")
@@ -45,4 +49,8 @@ for (f, n), w in lines.most_common(top):
         p = os.path.join(ROOT, "fo-rma_b200", "csrc", f)
         src[f] = open(p).read().splitlines() if os.path.exists(p) else []
     text = src[f][n - 1].strip()[:90] if 0 < n <= len(src[f]) else ""
-    print(f"{f}:{n:<4d} {100 * w / tw:6.2f}%  active {linest[(f, n)] / max(w, 1):5.1f}  {text}")
+    print(f"{f}:{n:<4d} {100 * w / tw:6.2f}%  active {linest[(f, n)] / max(w, 1):5.1f}  stall {100 * stall[(f, n)] / max(ts, 1):5.2f}%  {text}")
+print("---- by stall samples")
+for (f, n), sm in stall.most_common(top // 2):
+    text = src.get(f, [])[n - 1].strip()[:90] if f in src and 0 < n <= len(src[f]) else ""
+    print(f"{f}:{n:<4d} stall {100 * sm / max(ts, 1):5.2f}%  instr {100 * lines[(f, n)] / tw:5.2f}%  {text}")
