@@ -91,6 +91,19 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
         uint32_t s = 0, depth = 0;
         bool alive = false;
         float3 o = f3(0.0f, 0.0f, 0.0f), d = o;
+        if (beam_culled(P.cam, P.scene, x, y, P.width, P.height)) {
+            // no primary ray of this pixel can hit anything: every sample is camera ray -> sky
+            for (; s < P.spp; ++s) {
+                rng.sample = P.sample_offset + s;
+                Rand4 r0 = rng.block(0, 0);
+                if (no_jitter) { r0.x = 0.5f; r0.y = 0.5f; }
+                const float u = (fx + r0.x) / fw;
+                const float v = (fy + r0.y) / fh;
+                camera_ray(P.cam, rng, r0, u, v, pinhole, o, d);
+                col = col + sky(d);  // tracer.rs:174 with get_color = tracer.rs:213-217
+            }
+            rays = P.spp;
+        }
         for (;;) {
             if (!alive) {
                 if (s >= P.spp) break;

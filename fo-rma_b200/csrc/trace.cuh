@@ -261,6 +261,43 @@ __device__ __forceinline__ void load_node(const float4* __restrict__ nodes, int 
         : "=f"(n2.x), "=f"(n2.y), "=f"(n2.z), "=f"(n2.w), "=f"(n3.x), "=f"(n3.y), "=f"(n3.z), "=f"(n3.w) : "l"(p + 2));
 }
 
+// Primary-beam cull, once per pixel.  Every primary ray of pixel (x, y) is (1 - tau) o + tau F, tau >= 0,
+// with o on the lens (|o - pos| <= r_o) and F on the pixel's patch of the focus plane (|F - F_c| <= r_F), so
+// it stays within |1 - tau| r_o + tau r_F <= r_o + tau (r_o + r_F) of the central ray pos + tau (F_c - pos).
+// If that growing ball never reaches the bounding sphere (C, R) of all spheres and triangles -
+//   A tau^2 + 2 B tau + Cq > 0 for all tau >= 0,  A = D.D - k^2, B = m.D - R' k, Cq = m.m - R'^2,
+//   D = F_c - pos, m = pos - C, k = r_o + r_F, R' = R + r_o -
+// no sample of the pixel can hit anything and get_color (tracer.rs:189-219) is its sky branch.  Evaluated
+// in f64 with R, r_o, r_F inflated by 2^-10 relative (+ 2^-12 of the distances involved): orders of magnitude
+// above the f32 rounding of camera.rs:62-72 and above the miss distance at which sphere.rs:25-29 / the
+// triangle test can still accept (see scene_culled).  NaN / inf -> false -> the full scan runs.
+__device__ __forceinline__ bool beam_culled(const forma_rt_camera& c, const SceneView& S, uint32_t x, uint32_t y,
+                                            uint32_t width, uint32_t height) {
+    if (S.n_planes != 0 || !(S.cull_r2 < FLT_MAX)) return false;
+    const double w = (double)width, h = (double)height;
+    const double sc = ((double)x + 0.5) / w, tc = ((double)(height - y) + 0.5) / h;
+    double D[3], m[3], lu = 0.0, lv = 0.0, lh = 0.0, lvv = 0.0;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const double Fc = (double)c.lower_left_corner[i] + sc * (double)c.horizontal[i] + tc * (double)c.vertical[i];
+        D[i] = Fc - (double)c.position[i];
+        m[i] = (double)c.position[i] - (double)S.cull_center[i];
+        lu += (double)c.u[i] * (double)c.u[i]; lv += (double)c.v[i] * (double)c.v[i];
+        lh += (double)c.horizontal[i] * (double)c.horizontal[i]; lvv += (double)c.vertical[i] * (double)c.vertical[i];
+    }
+    const double slack = 1.0 + 9.765625e-4;  // 2^-10
+    const double mm = m[0] * m[0] + m[1] * m[1] + m[2] * m[2];
+    const double R = sqrt((double)S.cull_r2);
+    const double dist = sqrt(mm) + R;
+    const double r_o = fabs((double)c.lens_radius) * (sqrt(lu) + sqrt(lv)) * slack + 2.44140625e-4 * dist;
+    const double r_F = 0.5 * (sqrt(lh) / w + sqrt(lvv) / h) * slack * slack + 2.44140625e-4 * sqrt(D[0] * D[0] + D[1] * D[1] + D[2] * D[2]);
+    const double k = r_o + r_F, Rp = R * slack + r_o + 2.44140625e-4 * dist;
+    const double A = D[0] * D[0] + D[1] * D[1] + D[2] * D[2] - k * k;
+    const double B = m[0] * D[0] + m[1] * D[1] + m[2] * D[2] - Rp * k;
+    const double Cq = mm - Rp * Rp;
+    return Cq > 0.0 && A > 0.0 && (B >= 0.0 || B * B < A * Cq);
+}
+
 // LBVH walk over the primitives the tree indexes (lbvh.cu).  Exactness: a child box is visited iff
 // the ray's interval through the PADDED box reaches [0, closest]; the pad
 //     coef(ray) * q(child) + eps,   coef = 2^-19 (|o - C|^2 + R^2),  q = max 1/r below the child

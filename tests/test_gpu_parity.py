@@ -119,6 +119,34 @@ def test_mixed_list_order_semantics():
     assert_render_equal(m, objs, cam, w, h, 8, 77)
 
 
+def test_primary_beam_cull_edges():
+    """render_kernel skips the scan for pixels whose whole primary beam (lens x pixel footprint) misses
+    the bounding sphere of the scene: cameras far away, close up, inside the bounding sphere, with a
+    fat lens, and grazing spheres at the silhouette must all stay bit-exact."""
+    rng = np.random.default_rng(11)
+    objs = []
+    for i in range(9):  # < 16 primitives: the scan kernel, no ground sphere -> a small bounding sphere
+        objs.append(sphere(rng.uniform(-1.5, 1.5, 3), rng.uniform(.2, .7), mat=int(rng.integers(0, 4)),
+                           col=rng.uniform(.2, .9, 3), fuzz=rng.uniform(0, .5), id=i))
+    objs.append(tri((-2, -2, 0), (2, -2, 0.5), (0, 2.5, -0.5), id=20))
+    objs = np.stack(objs)
+    w, h = 112, 72
+    for k, (eye, at, fov, lens) in enumerate([((0, 0, 9), (0, 0, 0), 40, None), ((6, 3, 4), (0.5, 0, 0), 25, 0.4),
+                                              ((0.2, 0.1, 0.3), (1, 0, 0), 90, None), ((0, 0, 2.6), (0, 3, 0), 60, 1.5),
+                                              ((30, 0, 0), (0, 2.2, 0), 8, None)]):
+        m = forma_b200.create_model(w, h, seed=50 + k)
+        m.scene.load_objects(objs)
+        cam = ob.camera_look(eye, at, (0, 1, 0), fov, w / h)
+        if lens is not None:
+            cam[22] = lens
+        m.scene.camera.set_array(cam)
+        assert_render_equal(m, objs, cam, w, h, 4, 50 + k)
+        ids_g, t_g = m.primary_hits()
+        ids_o, t_o = ob.primary_hits(objs, cam, w, h)
+        assert np.array_equal(ids_g, ids_o) and np.array_equal(bits(t_g), bits(t_o))
+        assert (ids_g < 0).any()  # there is sky in every view, so some beams are culled
+
+
 def test_flags_depth_and_sample_offset():
     w, h = 120, 80
     objs, cam = ob.builtin_scene(2), ob.camera_new(w, h)
