@@ -74,6 +74,7 @@ struct forma_rt {
     uint32_t refill = 16;     // lanes idle before a warp stops walking to refill them
     uint32_t leaf_batch = 8;  // walk_mode 1: lanes that must stop progressing before the warp looks at its waiting leaves
     int walk_mode = -1;       // -1: by tree size; 0: while-while steps, 1: convergent walk (one node per lane and iteration)
+    int fast_div = -1;   // div_const (trace.cuh): -1 not checked yet, 0 IEEE division, 1 verified multiply form
     uint32_t frame = 0;  // update() call counter -> sample index of the interactive frame
 
     // packed scene (host copies kept for re-upload after set_object)
@@ -562,6 +563,22 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
         // convergent one-node-per-iteration walk; shallow ones are leaf-heavy and want while-while steps
         P.walk_mode = c->walk_mode >= 0 ? (uint32_t)c->walk_mode : (c->stats.bvh_nodes >= 4096u ? 1u : 0u);
     }
+    if (c->fast_div < 0) {  // once per handle: width and height never change
+        c->fast_div = 0;
+        const char* env = std::getenv("FORMA_RT_FAST_DIV");
+        if (!env || std::atoi(env) != 0) {
+            CU_TRY(c->d_job.ensure(1));
+            CU_TRY(cudaMemsetAsync(c->d_job.p, 0, sizeof(unsigned int), stream));
+            CU_TRY(forma::launch_div_verify((float)c->width, (float)c->width + 1.0f, c->d_job.p, c->sm_count, stream));
+            CU_TRY(forma::launch_div_verify((float)c->height, (float)c->height + 1.0f, c->d_job.p, c->sm_count, stream));
+            unsigned int bad = 1;
+            CU_TRY(cudaMemcpyAsync(&bad, c->d_job.p, sizeof bad, cudaMemcpyDeviceToHost, stream));
+            CU_TRY(cudaStreamSynchronize(stream));
+            c->fast_div = bad == 0 ? 1 : 0;
+        }
+    }
+    P.inv_w = 1.0f / (float)c->width; P.inv_h = 1.0f / (float)c->height;
+    P.fast_div = (uint32_t)c->fast_div;
     uint32_t launches = 0;
     CU_TRY(cudaMemsetAsync(c->d_rays, 0, sizeof(unsigned long long), stream));
     CU_TRY(cudaEventRecord(c->ev_k0, stream));

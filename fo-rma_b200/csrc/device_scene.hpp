@@ -79,6 +79,8 @@ struct RenderParams {
     uint8_t* rgb;              // nullable
     float4* sum;               // nullable
     unsigned long long* rays;  // device counter
+    float inv_w, inv_h;        // RN(1 / width), RN(1 / height)
+    uint32_t fast_div;         // 1: div_const's multiply form was verified exhaustively for both divisors
     // ---- tree mode only (render_tree_kernel + accumulate_kernel, kernels.cu) ----
     float4* rad;               // [chunk sample][pixel] radiance of the finished paths of one chunk
     float4* acc;               // [pixel] running in-order sum across chunks

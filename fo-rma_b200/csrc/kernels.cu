@@ -82,6 +82,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
         const float fx = (float)x, fy = (float)(P.height - y);  // tracer.rs:171-172 (Q1: height - y)
         const float fw = (float)P.width, fh = (float)P.height;
         const bool no_jitter = P.flags & FORMA_RT_NO_JITTER, pinhole = P.flags & FORMA_RT_PINHOLE;
+        const bool fast_div = P.fast_div != 0u;
         // tracer.rs:168-175's sample loop and get_color's recursion (tracer.rs:189-219) as ONE flat
         // loop of closest-hit queries: a lane whose path ended starts the next sample of its own pixel
         // in the same iteration the other lanes spend on their next bounce, so a warp runs for the
@@ -92,15 +93,34 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
         bool alive = false;
         float3 o = f3(0.0f, 0.0f, 0.0f), d = o;
         if (beam_culled(P.cam, P.scene, x, y, P.width, P.height)) {
-            // no primary ray of this pixel can hit anything: every sample is camera ray -> sky
-            for (; s < P.spp; ++s) {
+            // No primary ray of this pixel can hit anything: every sample is camera ray -> sky.  One Philox
+            // block per iteration and lane: block 0 of the lane's next sample, or - when its lens try was
+            // rejected (utility.rs:4-13) - the next retry block of the SAME sample, so the retries of some
+            // lanes ride along with the fresh samples of the others instead of costing the warp a pass of
+            // their own.  Each lane still adds its samples in order.
+            uint32_t blk = 0;
+            float xu = 0.0f, xv = 0.0f;
+            while (s < P.spp) {
                 rng.sample = P.sample_offset + s;
-                Rand4 r0 = rng.block(0, 0);
-                if (no_jitter) { r0.x = 0.5f; r0.y = 0.5f; }
-                const float u = (fx + r0.x) / fw;
-                const float v = (fy + r0.y) / fh;
-                camera_ray(P.cam, rng, r0, u, v, pinhole, o, d);
-                col = col + sky(d);  // tracer.rs:174 with get_color = tracer.rs:213-217
+                const Rand4 r = rng.block(0, blk);
+                float px, py;
+                bool ok;
+                if (blk == 0) {
+                    xu = no_jitter ? 0.5f : r.x; xv = no_jitter ? 0.5f : r.y;
+                    px = 2.0f * r.z - 1.0f; py = 2.0f * r.w - 1.0f;
+                    ok = pinhole || !(px * px + py * py >= 1.0f);
+                } else {
+                    ok = lens_retry(r, px, py);
+                }
+                if (ok) {
+                    const float u = div_const(fx + xu, fw, P.inv_w, fast_div);  // tracer.rs:171
+                    const float v = div_const(fy + xv, fh, P.inv_h, fast_div);  // tracer.rs:172
+                    camera_ray_at(P.cam, px, py, u, v, pinhole, o, d);
+                    col = col + sky(d);  // tracer.rs:174 with get_color = tracer.rs:213-217
+                    ++s; blk = 0;
+                } else {
+                    ++blk;
+                }
             }
             rays = P.spp;
         }
@@ -110,8 +130,8 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
                 rng.sample = P.sample_offset + s;
                 Rand4 r0 = rng.block(0, 0);
                 if (no_jitter) { r0.x = 0.5f; r0.y = 0.5f; }
-                const float u = (fx + r0.x) / fw;
-                const float v = (fy + r0.y) / fh;
+                const float u = div_const(fx + r0.x, fw, P.inv_w, fast_div);
+                const float v = div_const(fy + r0.y, fh, P.inv_h, fast_div);
                 camera_ray(P.cam, rng, r0, u, v, pinhole, o, d);
                 depth = 0;
                 alive = true;
@@ -263,8 +283,8 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
                     slot = k * (P.width * P.height) + rng.pixel;
                     Rand4 r0 = rng.block(0, 0);
                     if (no_jitter) { r0.x = 0.5f; r0.y = 0.5f; }
-                    const float u = ((float)jx + r0.x) / fw;                    // tracer.rs:171
-                    const float v = ((float)(P.height - jy) + r0.y) / fh;       // tracer.rs:172 (Q1: height - y)
+                    const float u = div_const((float)jx + r0.x, fw, P.inv_w, P.fast_div != 0u);                // tracer.rs:171
+                    const float v = div_const((float)(P.height - jy) + r0.y, fh, P.inv_h, P.fast_div != 0u);   // tracer.rs:172 (Q1: height - y)
                     camera_ray(P.cam, rng, r0, u, v, pinhole, o, d);
                     depth = 0;
                     phase = kStart;
@@ -424,6 +444,25 @@ __global__ void reduce_tonemap_kernel(const __grid_constant__ PeerPtrs peers, in
             rgb[3 * i + 2] = (uint8_t)as_u8(sqrtf(c.z) * 255.0f);
         }
     }
+}
+
+// Exhaustive check of div_const for divisor b: every f32 numerator in {0} U [2^-24, hi] (the kernels form
+// (x + xi) and ((height - y) + xi) with xi a multiple of 2^-24 in [0, 1), so nothing else can occur).
+__global__ void div_verify_kernel(float b, float y, uint32_t hi_bits, unsigned int* __restrict__ mismatches) {
+    const uint32_t lo_bits = 0x33800000u;  // 2^-24
+    unsigned int bad = 0;
+    for (uint64_t i = lo_bits + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i <= hi_bits;
+         i += (uint64_t)gridDim.x * blockDim.x) {
+        const float n = __uint_as_float((uint32_t)i);
+        bad += __float_as_uint(div_const(n, b, y, true)) != __float_as_uint(n / b);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) bad += __float_as_uint(div_const(0.0f, b, y, true)) != __float_as_uint(0.0f / b);
+    if (bad) atomicAdd(mismatches, bad);
+}
+
+cudaError_t launch_div_verify(float b, float hi, unsigned int* d_mismatches, int sm_count, cudaStream_t stream) {
+    div_verify_kernel<<<sm_count * 8, 256, 0, stream>>>(b, 1.0f / b, __builtin_bit_cast(uint32_t, hi), d_mismatches);
+    return cudaGetLastError();
 }
 
 // ---- launchers -------------------------------------------------------------------------------------

@@ -102,30 +102,46 @@ __device__ __forceinline__ float schlick(float cosine, float ref_idx) {
 // ---- camera ray (camera.rs:62-72) ------------------------------------------------------------------
 // `r0` is block 0 of slot 0: (xi_u, xi_v, lens try 0).  Further lens tries: block j >= 1 holds tries
 // 2j-1 (x,y) and 2j (z,w).
-__device__ __forceinline__ void camera_ray(const forma_rt_camera& c, const PathRng& rng, const Rand4& r0, float s,
-                                           float t, bool pinhole, float3& origin, float3& dir) {
+// camera.rs:63-71 for an accepted lens sample (px, py)
+__device__ __forceinline__ void camera_ray_at(const forma_rt_camera& c, float px, float py, float s, float t,
+                                              bool pinhole, float3& origin, float3& dir) {
     float3 offset = f3(0.0f, 0.0f, 0.0f);
     if (!pinhole) {
-        float px = 2.0f * r0.z - 1.0f, py = 2.0f * r0.w - 1.0f;
-        // utility.rs:4-13: retry while dot(p,p) >= 1 with p.z = 0.  (x*x + y*y) + 0*0 == x*x + y*y: a sum
-        // of squares is never -0.  Both tries of a retry block are evaluated branch-free.
-        if (px * px + py * py >= 1.0f) {
-            uint32_t blk = 0;
-            for (;;) {
-                const Rand4 r = rng.block(0, ++blk);
-                px = 2.0f * r.x - 1.0f; py = 2.0f * r.y - 1.0f;
-                const float qx = 2.0f * r.z - 1.0f, qy = 2.0f * r.w - 1.0f;
-                const bool ok1 = !(px * px + py * py >= 1.0f), ok2 = !(qx * qx + qy * qy >= 1.0f);
-                if (!ok1) { px = qx; py = qy; }
-                if (ok1 || ok2) break;
-            }
-        }
         float rdx = c.lens_radius * px, rdy = c.lens_radius * py;  // camera.rs:63
         offset = rdx * f3(c.u) + rdy * f3(c.v);                      // camera.rs:64
     }
     float3 pos = f3(c.position);
     origin = pos + offset;                                           // camera.rs:67
     dir = f3(c.lower_left_corner) + s * f3(c.horizontal) + t * f3(c.vertical) - pos - offset;  // :68-70
+}
+
+// utility.rs:4-13 on one RETRY block (tries 2j-1 and 2j, evaluated branch-free): true when one is
+// accepted.  dot(p,p) with p.z = 0: (x*x + y*y) + 0*0 == x*x + y*y, a sum of squares is never -0.
+__device__ __forceinline__ bool lens_retry(const Rand4& r, float& px, float& py) {
+    px = 2.0f * r.x - 1.0f; py = 2.0f * r.y - 1.0f;
+    const float qx = 2.0f * r.z - 1.0f, qy = 2.0f * r.w - 1.0f;
+    const bool ok1 = !(px * px + py * py >= 1.0f), ok2 = !(qx * qx + qy * qy >= 1.0f);
+    if (!ok1) { px = qx; py = qy; }
+    return ok1 || ok2;
+}
+
+__device__ __forceinline__ void camera_ray(const forma_rt_camera& c, const PathRng& rng, const Rand4& r0, float s,
+                                           float t, bool pinhole, float3& origin, float3& dir) {
+    float px = 2.0f * r0.z - 1.0f, py = 2.0f * r0.w - 1.0f;
+    if (!pinhole && px * px + py * py >= 1.0f) {
+        uint32_t blk = 0;
+        while (!lens_retry(rng.block(0, ++blk), px, py)) {}
+    }
+    camera_ray_at(c, px, py, s, t, pinhole, origin, dir);
+}
+
+// n / b for a launch-constant divisor b with y = RN(1 / b): q0 = RN(n y), q = RN(q0 + RN(n - q0 b) y)
+// (Markstein's correction).  The host enables `fast` only after div_verify_kernel has compared this
+// with IEEE division for EVERY f32 numerator the kernels can form for this b (kernels.cu).
+__device__ __forceinline__ float div_const(float n, float b, float y, bool fast) {
+    if (!fast) return n / b;
+    const float q0 = n * y;
+    return __fmaf_rn(__fmaf_rn(-q0, b, n), y, q0);
 }
 
 // ---- closest hit (tracer.rs:190-200 over sphere.rs:23-51, plane.rs:24-44, triangle extension) ------
