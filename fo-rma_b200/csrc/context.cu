@@ -70,10 +70,9 @@ struct forma_rt {
     forma::Scene scene;
     bool scene_dirty = true;
     bool stats_pending = false;
-    // render_tree_kernel tuning (FORMA_RT_REFILL / FORMA_RT_LEAF_BATCH / FORMA_RT_WALK_MODE override; not part of the ABI)
+    // render_tree_kernel tuning (FORMA_RT_REFILL / FORMA_RT_LEAF_BATCH override; not part of the ABI)
     uint32_t refill = 16;     // lanes idle before a warp stops walking to refill them
-    uint32_t leaf_batch = 8;  // walk_mode 1: lanes that must stop progressing before the warp looks at its waiting leaves
-    int walk_mode = -1;       // -1: by tree size; 0: while-while steps, 1: convergent walk (one node per lane and iteration)
+    uint32_t leaf_batch = 8;  // lanes that must stop progressing before the warp looks at its waiting leaves
     int fast_div = -1;   // div_const (trace.cuh): -1 not checked yet, 0 IEEE division, 1 verified multiply form
     uint32_t frame = 0;  // update() call counter -> sample index of the interactive frame
 
@@ -198,24 +197,29 @@ int upload_scene(forma_rt* c) {
             hi[NS + t] = {std::max({x[0], x[1], x[2]}), std::max({y[0], y[1], y[2]}), std::max({z[0], z[1], z[2]})};
         }
         auto extent = [&](int i) { return std::max({hi[i].x - lo[i].x, hi[i].y - lo[i].y, hi[i].z - lo[i].z}); };
-        // "big" primitives (a ground sphere of radius 1000 among unit spheres, a floor quad) would wreck the
-        // Morton grid and the upper tree levels: they are scanned linearly instead.  Only for large scenes.
+        // Outsized primitives (a ground sphere of radius 1000 among unit spheres, a 1000-unit floor quad) would
+        // blow up the walk's sphere pad (it scales with the squared radius of the tree's bounding sphere) and
+        // the Morton grid: they are scanned linearly instead.  "Outsized" = 4x larger than everything else
+        // together; merely large primitives stay in the tree (profiles/r01t: with the old 0.25 E rule 162 of
+        // scene_01's 350 triangles were scanned by every ray, 85 % of config A's instructions).
         std::vector<char> big(N, 0);
-        if (N >= 64) {
-            for (int pass = 0; pass < 3; ++pass) {
-                V3 ulo{FLT_MAX, FLT_MAX, FLT_MAX}, uhi{-FLT_MAX, -FLT_MAX, -FLT_MAX};
-                for (int i = 0; i < N; ++i) if (!big[i] && std::isfinite(extent(i))) {
-                    ulo = {std::min(ulo.x, lo[i].x), std::min(ulo.y, lo[i].y), std::min(ulo.z, lo[i].z)};
-                    uhi = {std::max(uhi.x, hi[i].x), std::max(uhi.y, hi[i].y), std::max(uhi.z, hi[i].z)};
-                }
-                const float E = std::max({uhi.x - ulo.x, uhi.y - ulo.y, uhi.z - ulo.z});
-                bool changed = false;
-                for (int i = 0; i < N; ++i) if (!big[i] && !(extent(i) <= 0.25f * E)) { big[i] = 1; changed = true; }
-                if (!changed) break;
+        if (N >= 16) {
+            // largest first: a prefix of the order is outsized iff its smallest member exceeds 4x the box around all the others
+            std::vector<int> order;
+            for (int i = 0; i < N; ++i) if (std::isfinite(extent(i))) order.push_back(i);
+            std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return extent(x) > extent(y); });
+            const int M = (int)order.size();
+            std::vector<float> rest(M + 1, 0.0f);  // rest[k] = extent of the union of order[k..M)
+            V3 ulo{FLT_MAX, FLT_MAX, FLT_MAX}, uhi{-FLT_MAX, -FLT_MAX, -FLT_MAX};
+            for (int k = M - 1; k >= 0; --k) {
+                const int i = order[k];
+                ulo = {std::min(ulo.x, lo[i].x), std::min(ulo.y, lo[i].y), std::min(ulo.z, lo[i].z)};
+                uhi = {std::max(uhi.x, hi[i].x), std::max(uhi.y, hi[i].y), std::max(uhi.z, hi[i].z)};
+                rest[k] = std::max({uhi.x - ulo.x, uhi.y - ulo.y, uhi.z - ulo.z});
             }
-            int nbig = 0;
-            for (int i = 0; i < N; ++i) nbig += big[i];
-            if (nbig > 256 || N - nbig < 2) std::fill(big.begin(), big.end(), 0);
+            int nbig = 0;  // the longest prefix (<= 64) whose smallest member is still 4x larger than all the rest together
+            for (int k = 1; k <= 64 && k + 2 <= M; ++k) if (extent(order[k - 1]) > 4.0f * rest[k]) nbig = k;
+            for (int k = 0; k < nbig; ++k) big[order[k]] = 1;
         }
         for (int i = 0; i < N; ++i) if (!std::isfinite(extent(i))) big[i] = 1;  // NaN/inf geometry stays on the exact scan
         // stable partition of the packed arrays: big first
@@ -401,10 +405,6 @@ int forma_rt_create(const forma_rt_options* opts, uint32_t width, uint32_t heigh
         const int v = std::atoi(r);
         if (v >= 1 && v <= 32) c->leaf_batch = (uint32_t)v;
     }
-    if (const char* r = std::getenv("FORMA_RT_WALK_MODE")) {
-        const int v = std::atoi(r);
-        if (v >= 0 && v <= 1) c->walk_mode = v;
-    }
     // Scene::new (scene.rs:10-15): Camera::new + get_simple_scene
     c->scene.camera = forma::Camera::create(width, height);
     c->scene.objects = forma::builtin_scene(0);
@@ -559,9 +559,6 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
         P.rad = c->d_rad.p; P.acc = c->d_acc.p; P.job_counter = c->d_job.p;
         P.rad_chunk = (uint32_t)chunk;
         P.refill = c->refill; P.leaf_batch = c->leaf_batch;
-        // measured (profiles/r01k_sweep.txt): deep trees spend their time at internal nodes and want the
-        // convergent one-node-per-iteration walk; shallow ones are leaf-heavy and want while-while steps
-        P.walk_mode = c->walk_mode >= 0 ? (uint32_t)c->walk_mode : (c->stats.bvh_nodes >= 4096u ? 1u : 0u);
     }
     if (c->fast_div < 0) {  // once per handle: width and height never change
         c->fast_div = 0;

@@ -87,8 +87,7 @@ struct RenderParams {
     unsigned int* job_counter; // next (pixel, sample) job of the chunk
     uint32_t rad_chunk;        // capacity of `rad` in samples
     uint32_t chunk_base, chunk_k; // samples [chunk_base, chunk_base + chunk_k) are traced by this launch
-    uint32_t walk_mode;        // 0: while-while steps, 1: convergent walk (one node per lane and iteration)
-    uint32_t leaf_batch;       // walk_mode 1: lanes that must stop before the warp looks at its waiting leaves
+    uint32_t leaf_batch;       // lanes that must stop before the warp looks at its waiting leaves
     uint32_t refill;           // refill a warp's finished lanes once this many are idle
 };
 

@@ -312,14 +312,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
         }
         if (__ballot_sync(kFull, !lane_done) == 0u) break;  // the queue is empty and every lane has finished
         // ---- E. walk until enough lanes are idle to be worth refilling
-        if (P.walk_mode == 0u) {
-            for (;;) {
-                if (phase == kWalk && !walk_step(S, sph, tri, o, d, a, W, wstack, h, w)) phase = kShade;
-                const unsigned walking = __ballot_sync(kFull, phase == kWalk);
-                const unsigned idle = __ballot_sync(kFull, !lane_done && phase != kWalk);
-                if (walking == 0u || __popc(idle) >= (int)P.refill) break;
-            }
-        } else {
+        {
             // Convergent walk: per iteration every walking lane takes ONE stack entry (if it needs one)
             // and tests ONE internal node, so lanes never wait for each other inside a node or a pop
             // loop.  Lanes that reach a leaf, finish or idle stop progressing; the warp looks at them only
@@ -336,7 +329,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
                         if (__int_as_float(e.y) <= h.closest) W.node = e.x;  // else: stays kWalkPop
                     }
                 }
-                if (walking && W.node >= 0) walk_inner<true>(S, W, wstack, h.closest);
+                if (walking && W.node >= 0) walk_inner(S, W, wstack, h.closest);
                 const bool busy = walking && (W.node >= 0 || W.node == kWalkPop);
                 const int stopped = 32 - __popc(__ballot_sync(kFull, busy));
                 if (stopped < wake_at) continue;

@@ -377,11 +377,10 @@ __device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __
 }
 
 // ---- resumable LBVH walk (render_tree_kernel) ------------------------------------------------------
-// The same padded walk as bvh_closest, cut into steps so that a warp can stop walking when enough
-// of its lanes have finished, refill those lanes with their next ray, and resume ("while-while"
-// traversal with ray regeneration).  One step = descend through internal nodes until a leaf is the
-// current node, test that leaf's primitive, pop.  Stack entries carry the entry distance of the
-// pushed child so a pop skips subtrees that the hits found meanwhile have put out of range.
+// The same padded walk as bvh_closest, cut into single-node steps so that a warp can advance all its
+// lanes together, stop when enough of them have finished, refill those with their next ray, and resume.
+// Stack entries carry the entry distance of the pushed child so that taking an entry skips subtrees
+// that the hits found meanwhile have put out of range.
 constexpr int kWalkDone = (int)0x80000000;  // never a leaf code: leaves are ~l with l < 2^31 - 2
 constexpr int kWalkPop = (int)0x80000001;   // convergent walk: this lane takes its next node from the stack
 
@@ -418,17 +417,8 @@ struct WalkStack {
     __device__ __forceinline__ int2 at(int sp) const { return sp < kSmemStack ? smem[sp * kWalkBlock] : local[sp - kSmemStack]; }
 };
 
-__device__ __forceinline__ int walk_pop(Walk& W, const WalkStack& stack, float closest) {
-    while (W.sp > 0) {
-        const int2 e = stack.at(--W.sp);
-        if (__int_as_float(e.y) <= closest) return e.x;  // <=: an equal t with a smaller list index still wins
-    }
-    return kWalkDone;
-}
-
-// One internal node: test both child boxes, descend into the nearer hit child (pushing the other) or pop
-// (LAZY_POP: leave the pop to the caller's next iteration).
-template <bool LAZY_POP = false>
+// One internal node: test both child boxes, descend into the nearer hit child (pushing the other), or ask
+// for the next stack entry (kWalkPop, taken by the caller's next iteration).
 __device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, const WalkStack& stack, float closest) {
     const int node = W.node;
     const float eps = S.bvh_eps;
@@ -455,27 +445,7 @@ __device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, const Wa
         stack.push(W.sp++, make_int2(swap ? cL : cR, __float_as_int(swap ? nearL : nearR)));
     } else if (hitL) W.node = cL;
     else if (hitR) W.node = cR;
-    else W.node = LAZY_POP ? kWalkPop : walk_pop(W, stack, closest);
-}
-
-// One leaf: test its primitive, pop.
-__device__ __forceinline__ void walk_leaf(const SceneView& S, const float4* __restrict__ sph,
-                                          const float4* __restrict__ tri, float3 o, float3 d, float a, Walk& W,
-                                          const WalkStack& stack, HitState& h, Winner& w) {
-    const int p = ~W.node;  // leaf codes are the complemented unified primitive index
-    if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w);
-    else try_triangle(S, tri, p - S.n_spheres, o, d, h, w);
-    W.node = walk_pop(W, stack, h.closest);
-}
-
-// One "while-while" step: internal nodes until a leaf is the current node, that leaf, pop.
-// Returns false once the walk is complete.
-__device__ __forceinline__ bool walk_step(const SceneView& S, const float4* __restrict__ sph,
-                                          const float4* __restrict__ tri, float3 o, float3 d, float a, Walk& W,
-                                          const WalkStack& stack, HitState& h, Winner& w) {
-    while (W.node >= 0) walk_inner(S, W, stack, h.closest);
-    if (W.node != kWalkDone) walk_leaf(S, sph, tri, o, d, a, W, stack, h, w);
-    return W.node != kWalkDone;
+    else W.node = kWalkPop;
 }
 
 // MODE selects what a kernel instantiation carries: the brute-force scan with the primitives staged

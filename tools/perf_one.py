@@ -1,0 +1,16 @@
+"""One render of one case (for ncu): python tools/perf_one.py A|B|D [spp]"""
+import os, sys
+sys.argv = [sys.argv[0]] + sys.argv[1:]
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import forma_b200
+which = sys.argv[1]
+S = os.path.join(ROOT, "tests", "golden", "scenes")
+name, w, h, spp = {"A": ("scene_01", 600, 600, 50), "B": ("scene_05", 1920, 1080, 4), "C": ("scene_09", 1920, 1080, 256)}[which]
+if len(sys.argv) > 2: spp = int(sys.argv[2])
+m = forma_b200.create_model(w, h, seed=0)
+m.scene.load_json(open(os.path.join(S, name + ".json")).read()); m.scene.camera.use_json()
+for _ in range(2):
+    m.render(spp)
+    st = m.stats()
+print(which, st.kernel_ms, st.rays)
