@@ -261,12 +261,54 @@ def run_ours(args):
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": npix * 3 + 8,
                "api": "forma_rt_load_json + forma_rt_camera_json + forma_rt_render (host RGB8 buffer, pinned)"}
 
+    others = None
+    if world == 1 and not args.no_other_configs:
+        others = other_configs(local)
     if rank == 0:
         emit(args, world, value, ms_per_step, rays_step, kern_ms, st, clk.summary(), e2e, launches, t_wall,
-             ex.mode if ex else ("NCCL reduce + tonemap" if world > 1 else None))
+             ex.mode if ex else ("NCCL reduce + tonemap" if world > 1 else None), others)
     if dist:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def other_configs(device):
+    """BASELINE.json's other single-GPU configs through the host-facing API (untimed part of the run; parity
+    for each is in tests/): kernel time from the library's CUDA events, total = kernel + D2H of the result."""
+    import importlib.util
+    import forma_b200
+    scenes = os.path.dirname(SCENE)
+    out = {}
+
+    def best(m, fn, reps=3):
+        b = None
+        for _ in range(reps):
+            fn()
+            st = m.stats()
+            if b is None or st.kernel_ms < b.kernel_ms:
+                b = st
+        return b
+
+    m = forma_b200.create_model(600, 600, device=device, seed=SEED)
+    m.scene.load_json(open(os.path.join(scenes, "scene_01.json")).read()); m.scene.camera.use_json()
+    st = best(m, lambda: m.render(50, max_depth=DEPTH))
+    out["A scene_01 600x600 50 spp (JSON camera)"] = {"kernel_ms": round(st.kernel_ms, 3), "total_ms": round(st.total_ms, 3),
+                                                     "rays": int(st.rays), "mrays_s": round(st.rays / st.kernel_ms / 1e3, 1)}
+    m.close()
+    m = forma_b200.create_model(W, H, device=device, seed=SEED)
+    m.scene.load_json(open(os.path.join(scenes, "scene_05.json")).read()); m.scene.camera.use_json()
+    st = best(m, lambda: m.primary_hits())
+    out["B scene_05 1920x1080 primary hit id/t dump"] = {"kernel_ms": round(st.kernel_ms, 3), "total_ms": round(st.total_ms, 3),
+                                                        "rays": int(st.rays), "mrays_s": round(st.rays / st.kernel_ms / 1e3, 1)}
+    spec = importlib.util.spec_from_file_location("gen", os.path.join(ROOT, "python-extras", "sphere_scene_generator.py"))
+    gen = importlib.util.module_from_spec(spec); spec.loader.exec_module(gen)
+    m.scene.load_json(json.dumps(gen.generate(100_000))); m.scene.camera.use_json()
+    st = best(m, lambda: m.render(64, max_depth=DEPTH), reps=2)
+    out["D 100k spheres 1920x1080 64 spp (LBVH)"] = {"kernel_ms": round(st.kernel_ms, 3), "total_ms": round(st.total_ms, 3),
+                                                    "rays": int(st.rays), "mrays_s": round(st.rays / st.kernel_ms / 1e3, 1),
+                                                    "bvh_nodes": int(st.bvh_nodes)}
+    m.close()
+    return out
 
 
 def _d2h(host_np, d_ptr, nbytes):
@@ -274,7 +316,7 @@ def _d2h(host_np, d_ptr, nbytes):
     rt.cudaMemcpy(host_np.ctypes.data, d_ptr, nbytes, rt.cudaMemcpyKind.cudaMemcpyDeviceToHost)
 
 
-def emit(args, world, value, ms_per_step, rays_step, kern_ms, st, clocks, e2e, launches, t_wall, exchange):
+def emit(args, world, value, ms_per_step, rays_step, kern_ms, st, clocks, e2e, launches, t_wall, exchange, others=None):
     peaks, src = measured_peaks()
     paths_rank = W * H * SPP
     rays_rank = rays_step / world
@@ -311,6 +353,8 @@ def emit(args, world, value, ms_per_step, rays_step, kern_ms, st, clocks, e2e, l
                     "peak_gbs": peaks.get("hbm_gbs"), "frac": round(hbm_bytes / (kern_ms * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6650.0), 6) if kern_ms > 0 else None}},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
     }
+    if others:
+        line["other_configs"] = others
     if world == 1 and not args.no_cpu_baseline:
         cores = host_cores()
         v1, dt1, _ = cpu_sample(1, 8)           # faithful: render/save_image are single-threaded (tracer.rs:57-81,160-187)
@@ -329,6 +373,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the untimed A / B / D measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

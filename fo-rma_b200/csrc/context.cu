@@ -71,7 +71,7 @@ struct forma_rt {
     bool scene_dirty = true;
     bool stats_pending = false;
     // render_tree_kernel tuning (FORMA_RT_REFILL / FORMA_RT_LEAF_BATCH override; not part of the ABI)
-    uint32_t refill = 16;     // lanes idle before a warp stops walking to refill them
+    uint32_t refill = 20;     // lanes idle before a warp stops walking to refill them
     uint32_t leaf_batch = 8;  // lanes that must stop progressing before the warp looks at its waiting leaves
     int fast_div = -1;   // div_const (trace.cuh): -1 not checked yet, 0 IEEE division, 1 verified multiply form
     uint32_t frame = 0;  // update() call counter -> sample index of the interactive frame
@@ -284,6 +284,8 @@ int upload_scene(forma_rt* c) {
     v.seg0 = segments.empty() ? Segment{0, 0, 0, 0, -1} : segments[0];
     v.n_spheres = (int)ns; v.n_tris = (int)nt; v.n_planes = (int)np;
     v.bvh_nodes = nullptr;
+    v.finite_materials = 1;
+    for (const float4& mt : material) if (!(std::isfinite(mt.x) && std::isfinite(mt.y) && std::isfinite(mt.z))) v.finite_materials = 0;
 
     {   // closest_hit's conservative cull: bounding sphere of the box around every sphere and triangle
         V3 ulo{FLT_MAX, FLT_MAX, FLT_MAX}, uhi{-FLT_MAX, -FLT_MAX, -FLT_MAX};

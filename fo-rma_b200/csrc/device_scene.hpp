@@ -48,6 +48,7 @@ struct SceneView {
     const float4* bvh_nodes;   // 4 float4 per internal node: see lbvh.cu
     const int* bvh_prim;       // unified primitive index (< n_spheres: sphere) of sorted leaf l
     int big_spheres, big_tris; // with a tree: the first big_* packed primitives are scanned linearly
+    int finite_materials;      // 1: every colour component of every list entry is finite (see black_path)
     int tree_seg;              // with a tree: index of the one segment that holds spheres / triangles
     float bvh_center[3];       // bounding sphere of everything the tree indexes
     float bvh_r2;              // its radius squared

@@ -152,6 +152,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
                 }
             }
             if (done) {
+                if (black_path(P.scene, pc)) depth = 0;
                 while (depth > 0) {  // tracer.rs:206-207 on the way back up
                     --depth;
                     pc = attenuation(P.scene, stack[depth]) * pc;
@@ -246,6 +247,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
             }
             phase = kStart;
             if (done) {
+                if (black_path(S, pc)) depth = 0;
                 while (depth > 0) {  // tracer.rs:206-207 on the way back up
                     --depth;
                     pc = attenuation(S, astack[depth]) * pc;

@@ -175,6 +175,15 @@ def test_nan_propagation_matches():
     rgb_o, lin_o, _ = ob.render(objs, ob.camera_new(w, h), w, h, 2, seed=1)
     assert np.isnan(lin_o).any() and np.array_equal(np.isnan(lin_o), np.isnan(lin_g[..., :3]))
     assert np.array_equal(rgb_g, rgb_o) and (rgb_g[np.isnan(lin_o)] == 0).all()
+    # a path cut at max_depth is black, but 0 x inf on the way back up is NaN: the kernels may skip the walk
+    # back up for black paths only when every colour is finite
+    objs = np.stack([sphere((0, -1000.5, -1), 1000.0, mat=0, col=(.5, .5, .5)), sphere((0, 0, -1), 0.5, mat=0, col=(float("inf"), .5, .5))])
+    m.scene.load_objects(objs)
+    rgb_g, lin_g = m.render(2, max_depth=1, want_linear=True)
+    rgb_o, lin_o, _ = ob.render(objs, ob.camera_new(w, h), w, h, 2, seed=1, max_depth=1)
+    nan = np.isnan(lin_o)  # NaN payloads differ between SSE (0xFFC00000) and CUDA (0x7FFFFFFF): compare the pattern
+    assert nan.any() and np.array_equal(nan, np.isnan(lin_g[..., :3])) and np.array_equal(rgb_g, rgb_o)
+    assert np.array_equal(bits(np.where(nan, 0, lin_g[..., :3])), bits(np.where(nan, 0, lin_o)))
 
 
 def test_save_image_png(tmp_path):  # tracer.rs:160-187
