@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libforma_rt.so")
 
 OK, EINVAL, EJSON, ECUDA, EIO, ENOMEM = 0, -1, -2, -3, -4, -5
-NO_JITTER, PINHOLE, HOST_ONLY = 1, 2, 4
+NO_JITTER, PINHOLE, HOST_ONLY, SRGB_OUT = 1, 2, 4, 8
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_LBVH = 0, 1, 2
 SPHERE, PLANE, TRIANGLE = 0, 1, 2
 
@@ -69,6 +69,11 @@ SYMBOLS = {
     "forma_rt_camera_get": (_int, [_vp, ctypes.POINTER(Camera)]),
     "forma_rt_camera_set": (_int, [_vp, ctypes.POINTER(Camera)]),
     "forma_rt_update": (_int, [_vp, ctypes.c_uint8, ctypes.c_float, _vp]),
+    "forma_rt_accumulate": (_int, [_vp, _u32, _u32, _vp, _vp, ctypes.POINTER(_u32)]),
+    "forma_rt_accumulate_reset": (_int, [_vp]),
+    "forma_rt_update_progressive": (_int, [_vp, ctypes.c_uint8, ctypes.c_float, _vp, ctypes.POINTER(_u32)]),
+    "forma_rt_srgb_encode_device": (_int, [_vp, _vp, _sz, _vp]),
+    "forma_rt_srgb_table": (_int, [_vp]),
     "forma_rt_render": (_int, [_vp, _u32, _u32, _u32, _vp, _vp]),
     "forma_rt_save_image": (_int, [_vp, _u32, ctypes.c_char_p]),
     "forma_rt_primary_hits": (_int, [_vp, _vp, _vp]),
@@ -107,7 +112,7 @@ def lib() -> ctypes.CDLL:
         for name, (res, args) in SYMBOLS.items():
             fn = getattr(L, name)  # AttributeError here = header/library skew
             fn.restype, fn.argtypes = res, args
-        if L.forma_rt_abi_version() != 1:
+        if L.forma_rt_abi_version() != 2:
             raise ImportError("libforma_rt.so ABI version mismatch")
         _lib = L
     return _lib

@@ -88,6 +88,10 @@ struct forma_rt {
     DevBuf<float4> d_sum;
     DevBuf<int32_t> d_prim;
     DevBuf<float> d_t;
+    DevBuf<float4> d_prog;            // progressive mode: running f32 sum of prog_spp samples per pixel
+    uint32_t prog_spp = 0;
+    forma_rt_camera prog_cam{};       // camera the running sum belongs to
+    uint8_t srgb_lut[256];            // color_utils::srgb_encode as a table (color_utils.rs:49-66)
     DevBuf<float4> d_rad, d_acc;      // tree mode: per-path radiance of a chunk of samples, in-order running sum
     DevBuf<unsigned int> d_job;       // tree mode: job queue head
     unsigned long long* d_rays = nullptr;
@@ -105,7 +109,7 @@ struct forma_rt {
         d_spheres.release(); d_tris.release(); d_planes.release(); d_material.release();
         d_sphere_obj.release(); d_tri_obj.release(); d_plane_obj.release(); d_kindmat.release(); d_ids.release();
         d_segments.release(); d_rgb.release(); d_sum.release(); d_prim.release(); d_t.release();
-        d_rad.release(); d_acc.release(); d_job.release();
+        d_rad.release(); d_acc.release(); d_job.release(); d_prog.release();
         bvh.release();
         if (d_rays) cudaFree(d_rays);
         if (h_rays) cudaFreeHost(h_rays);
@@ -407,6 +411,7 @@ int forma_rt_create(const forma_rt_options* opts, uint32_t width, uint32_t heigh
         const int v = std::atoi(r);
         if (v >= 1 && v <= 32) c->leaf_batch = (uint32_t)v;
     }
+    forma::srgb_encode_table(c->srgb_lut);
     // Scene::new (scene.rs:10-15): Camera::new + get_simple_scene
     c->scene.camera = forma::Camera::create(width, height);
     c->scene.objects = forma::builtin_scene(0);
@@ -538,7 +543,8 @@ namespace {
 
 // One launch of the trace kernel on `stream`; outputs are device pointers.  Records kernel events.
 int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t max_depth, uint32_t flags,
-                     uint8_t* d_rgb, float4* d_sum, cudaStream_t stream) {
+                     uint8_t* d_rgb, float4* d_sum, cudaStream_t stream, const float4* d_prior = nullptr,
+                     uint32_t spp_prior = 0) {
     if (spp == 0) return fail(FORMA_RT_EINVAL, "render: spp must be >= 1");
     if (max_depth > (uint32_t)forma::kMaxDepthCap)
         return fail(FORMA_RT_EINVAL, "render: max_depth exceeds the attenuation stack (64; the reference uses 50)");
@@ -551,6 +557,7 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
     P.spp = spp; P.sample_offset = sample_offset; P.max_depth = max_depth; P.flags = flags;
     P.rk.expand(c->seed);
     P.rgb = d_rgb; P.sum = d_sum; P.rays = c->d_rays;
+    P.prior = d_prior; P.spp_prior = d_prior ? spp_prior : 0;
     if (P.scene.bvh_nodes) {  // tree mode: rad holds a chunk of samples of the frame, <= kRadBudget bytes
         const size_t npix = (size_t)c->width * c->height;
         size_t chunk = kRadBudget / (npix * sizeof(float4));
@@ -583,6 +590,10 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
     CU_TRY(cudaEventRecord(c->ev_k0, stream));
     CU_TRY(forma::launch_render(P, c->sm_count, stream, &launches));
     CU_TRY(cudaEventRecord(c->ev_k1, stream));
+    if (d_rgb && (flags & FORMA_RT_SRGB_OUT)) {
+        CU_TRY(forma::launch_srgb_encode(d_rgb, (size_t)c->width * c->height * 3, c->srgb_lut, c->sm_count, stream));
+        ++launches;
+    }
     c->stats.gpu_launches = launches;
     c->stats.paths = (uint64_t)c->width * c->height * spp;
     c->stats_pending = true;  // ray counter + kernel time are read back by whoever synchronises
@@ -591,17 +602,20 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
 
 // host-facing render: device buffers owned by the handle, D2H of what the caller asked for
 int render_to_host(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t max_depth, uint32_t flags,
-                   uint8_t* rgb, float* linear_rgba) {
+                   uint8_t* rgb, float* linear_rgba, bool progressive = false) {
     const size_t npix = (size_t)c->width * c->height;
     if (rgb) CU_TRY(c->d_rgb.ensure(npix * 3));
-    if (linear_rgba) CU_TRY(c->d_sum.ensure(npix));
+    if (linear_rgba && !progressive) CU_TRY(c->d_sum.ensure(npix));
+    if (progressive) CU_TRY(c->d_prog.ensure(npix));
     cudaStream_t s = c->stream;
     CU_TRY(cudaEventRecord(c->ev_begin, s));
-    int rc = render_on_device(c, spp, sample_offset, max_depth, flags, rgb ? c->d_rgb.p : nullptr,
-                              linear_rgba ? c->d_sum.p : nullptr, s);
+    // progressive: the handle's running sum is both the prior and the output (each pixel is read, then written, by one thread)
+    float4* d_sum = progressive ? c->d_prog.p : (linear_rgba ? c->d_sum.p : nullptr);
+    int rc = render_on_device(c, spp, sample_offset, max_depth, flags, rgb ? c->d_rgb.p : nullptr, d_sum, s,
+                              progressive && c->prog_spp > 0 ? c->d_prog.p : nullptr, c->prog_spp);
     if (rc) return rc;
     if (rgb) CU_TRY(cudaMemcpyAsync(rgb, c->d_rgb.p, npix * 3, cudaMemcpyDeviceToHost, s));
-    if (linear_rgba) CU_TRY(cudaMemcpyAsync(linear_rgba, c->d_sum.p, npix * sizeof(float4), cudaMemcpyDeviceToHost, s));
+    if (linear_rgba) CU_TRY(cudaMemcpyAsync(linear_rgba, d_sum, npix * sizeof(float4), cudaMemcpyDeviceToHost, s));
     CU_TRY(cudaMemcpyAsync(c->h_rays, c->d_rays, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     CU_TRY(cudaEventRecord(c->ev_end, s));
     CU_TRY(cudaStreamSynchronize(s));
@@ -629,6 +643,48 @@ int forma_rt_update(forma_rt* ctx, uint8_t keys, float delta_time, uint8_t* rgb)
     int rc = render_to_host(ctx, 1, ctx->frame, 50, ctx->flags, rgb, nullptr);  // tracer.rs:54, MAX_DEPTH :10
     if (rc == FORMA_RT_OK) ctx->frame++;
     return rc;
+}
+
+int forma_rt_accumulate_reset(forma_rt* ctx) {
+    NEED_CTX(ctx);
+    ctx->prog_spp = 0;
+    return FORMA_RT_OK;
+}
+
+int forma_rt_accumulate(forma_rt* ctx, uint32_t spp_more, uint32_t max_depth, uint8_t* rgb, float* linear_rgba,
+                        uint32_t* spp_total) {
+    NEED_DEV(ctx);
+    if ((uint64_t)ctx->prog_spp + spp_more > 0x7fffffffu) return fail(FORMA_RT_EINVAL, "forma_rt_accumulate: sample count overflow");
+    // samples [prog_spp, prog_spp + spp_more) continue the running sum: bit-identical to one render of the total
+    int rc = render_to_host(ctx, spp_more, ctx->prog_spp, max_depth, ctx->flags, rgb, linear_rgba, true);
+    if (rc) return rc;
+    ctx->prog_spp += spp_more;
+    ctx->prog_cam = ctx->scene.camera.c;
+    if (spp_total) *spp_total = ctx->prog_spp;
+    return FORMA_RT_OK;
+}
+
+int forma_rt_update_progressive(forma_rt* ctx, uint8_t keys, float delta_time, uint8_t* rgb, uint32_t* spp_total) {
+    NEED_DEV(ctx);
+    if (!rgb) return fail(FORMA_RT_EINVAL, "forma_rt_update_progressive: rgb is null");
+    ctx->scene.camera.orbit(forma::keys_to_delta(keys, delta_time));  // tracer.rs:31-52, every frame like the reference
+    // a still camera and an untouched scene keep refining the frame; anything else starts over at sample 0
+    if (ctx->scene_dirty || std::memcmp(&ctx->prog_cam, &ctx->scene.camera.c, sizeof(forma_rt_camera)) != 0) ctx->prog_spp = 0;
+    return forma_rt_accumulate(ctx, 1, 50, rgb, nullptr, spp_total);
+}
+
+int forma_rt_srgb_encode_device(forma_rt* ctx, void* d_rgb, size_t nbytes, void* stream) {
+    NEED_DEV(ctx);
+    if (!d_rgb) return fail(FORMA_RT_EINVAL, "forma_rt_srgb_encode_device: d_rgb is null");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    CU_TRY(forma::launch_srgb_encode((uint8_t*)d_rgb, nbytes, ctx->srgb_lut, ctx->sm_count, s));
+    return FORMA_RT_OK;
+}
+
+int forma_rt_srgb_table(uint8_t table[256]) {
+    if (!table) return fail(FORMA_RT_EINVAL, "forma_rt_srgb_table: table is null");
+    forma::srgb_encode_table(table);
+    return FORMA_RT_OK;
 }
 
 int forma_rt_save_image(forma_rt* ctx, uint32_t sample, const char* path) {

@@ -80,6 +80,8 @@ struct RenderParams {
     uint8_t* rgb;              // nullable
     float4* sum;               // nullable
     unsigned long long* rays;  // device counter
+    const float4* prior;       // nullable: per-pixel f32 sum of the spp_prior samples traced by earlier calls (progressive mode)
+    uint32_t spp_prior;        // the new samples continue that sum; the write-out averages over spp_prior + spp
     float inv_w, inv_h;        // RN(1 / width), RN(1 / height)
     uint32_t fast_div;         // 1: div_const's multiply form was verified exhaustively for both divisors
     // ---- tree mode only (render_tree_kernel + accumulate_kernel, kernels.cu) ----

@@ -35,11 +35,12 @@ __device__ __forceinline__ void stage_scene(const SceneView& S, const float4*& s
 // gamma, (c * 255.0) as u8 — the RGB8 tile staged in shared memory and stored as coalesced words.
 __device__ __forceinline__ void write_out(const RenderParams& P, float3 col, uint32_t x, uint32_t y, int lx, int ly,
                                           bool live, uint8_t (*tile_rgb)[kTileW * 3]) {
-    if (P.sum && live) P.sum[(size_t)x + (size_t)y * P.width] = make_float4(col.x, col.y, col.z, (float)P.spp);
+    const float n_spp = (float)(P.spp + P.spp_prior);
+    if (P.sum && live) P.sum[(size_t)x + (size_t)y * P.width] = make_float4(col.x, col.y, col.z, n_spp);
 
     if (P.rgb) {
         // tracer.rs:177-184: average in linear space, sqrt gamma, (c * 255.0) as u8
-        float3 c = col / (float)P.spp;
+        float3 c = col / n_spp;
         const uint32_t r = as_u8(sqrtf(c.x) * 255.0f), g = as_u8(sqrtf(c.y) * 255.0f), b = as_u8(sqrtf(c.z) * 255.0f);
         const bool full_tile = (blockIdx.x + 1) * kTileW <= P.width && (blockIdx.y + 1) * kTileH <= P.height &&
                                (P.width * 3u) % 4u == 0;
@@ -78,6 +79,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
     uint32_t rays = 0;
     float3 col = f3(0.0f, 0.0f, 0.0f);
     if (live) {
+        if (P.prior) col = xyz(P.prior[(size_t)x + (size_t)y * P.width]);  // progressive: continue tracer.rs:170-175's sum
         PathRng rng{P.rk, x + y * P.width, 0u};
         const float fx = (float)x, fy = (float)(P.height - y);  // tracer.rs:171-172 (Q1: height - y)
         const float fw = (float)P.width, fh = (float)P.height;
@@ -363,14 +365,16 @@ __global__ void accumulate_kernel(const __grid_constant__ RenderParams P, int fi
     for (size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x; p < npix; p += (size_t)gridDim.x * blockDim.x) {
         float3 col = f3(0.0f, 0.0f, 0.0f);
         if (!first) { const float4 c = P.acc[p]; col = f3(c.x, c.y, c.z); }
+        else if (P.prior) col = xyz(P.prior[p]);
         for (uint32_t k = 0; k < P.chunk_k; ++k) {
             const float4 r = P.rad[k * npix + p];
             col = col + f3(r.x, r.y, r.z);  // tracer.rs:174
         }
         if (!last) { P.acc[p] = make_float4(col.x, col.y, col.z, 0.0f); continue; }
-        if (P.sum) P.sum[p] = make_float4(col.x, col.y, col.z, (float)P.spp);
+        const float n_spp = (float)(P.spp + P.spp_prior);
+        if (P.sum) P.sum[p] = make_float4(col.x, col.y, col.z, n_spp);
         if (P.rgb) {
-            const float3 c = col / (float)P.spp;
+            const float3 c = col / n_spp;
             P.rgb[3 * p + 0] = (uint8_t)as_u8(sqrtf(c.x) * 255.0f);
             P.rgb[3 * p + 1] = (uint8_t)as_u8(sqrtf(c.y) * 255.0f);
             P.rgb[3 * p + 2] = (uint8_t)as_u8(sqrtf(c.z) * 255.0f);
@@ -441,6 +445,27 @@ __global__ void reduce_tonemap_kernel(const __grid_constant__ PeerPtrs peers, in
     }
 }
 
+static int stream_grid(uint64_t n, int sm_count);
+
+// color_utils::srgb_encode (color_utils.rs:49-66) on an RGB8 buffer: a u8 -> u8 map, so a 256-entry table
+// (built on the host, context.cu) applied to four bytes per thread-iteration.  HBM-bound: 1 B in + 1 B out.
+struct SrgbLut {
+    uint8_t v[256];
+};
+__global__ void srgb_encode_kernel(uint8_t* __restrict__ rgb, size_t nbytes, const __grid_constant__ SrgbLut lut) {
+    __shared__ uint8_t t[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) t[i] = lut.v[i];
+    __syncthreads();
+    const size_t nwords = nbytes / 4;
+    uint32_t* w = reinterpret_cast<uint32_t*>(rgb);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nwords; i += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t x = w[i];
+        w[i] = (uint32_t)t[x & 0xff] | ((uint32_t)t[(x >> 8) & 0xff] << 8) | ((uint32_t)t[(x >> 16) & 0xff] << 16) |
+               ((uint32_t)t[x >> 24] << 24);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (nbytes & 3)) { const size_t j = nwords * 4 + threadIdx.x; rgb[j] = t[rgb[j]]; }
+}
+
 // Exhaustive check of div_const for divisor b: every f32 numerator in {0} U [2^-24, hi] (the kernels form
 // (x + xi) and ((height - y) + xi) with xi a multiple of 2^-24 in [0, 1), so nothing else can occur).
 __global__ void div_verify_kernel(float b, float y, uint32_t hi_bits, unsigned int* __restrict__ mismatches) {
@@ -455,6 +480,15 @@ __global__ void div_verify_kernel(float b, float y, uint32_t hi_bits, unsigned i
     if (bad) atomicAdd(mismatches, bad);
 }
 
+cudaError_t launch_srgb_encode(uint8_t* rgb, size_t nbytes, const uint8_t lut[256], int sm_count, cudaStream_t stream) {
+    if (nbytes == 0) return cudaSuccess;
+    if (reinterpret_cast<uintptr_t>(rgb) & 3) return cudaErrorMisalignedAddress;
+    SrgbLut L;
+    for (int i = 0; i < 256; ++i) L.v[i] = lut[i];
+    srgb_encode_kernel<<<stream_grid(nbytes / 4 + 1, sm_count), 256, 0, stream>>>(rgb, nbytes, L);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_div_verify(float b, float hi, unsigned int* d_mismatches, int sm_count, cudaStream_t stream) {
     div_verify_kernel<<<sm_count * 8, 256, 0, stream>>>(b, 1.0f / b, __builtin_bit_cast(uint32_t, hi), d_mismatches);
     return cudaGetLastError();
@@ -463,7 +497,6 @@ cudaError_t launch_div_verify(float b, float hi, unsigned int* d_mismatches, int
 // ---- launchers -------------------------------------------------------------------------------------
 static dim3 tile_grid(uint32_t w, uint32_t h) { return dim3((w + kTileW - 1) / kTileW, (h + kTileH - 1) / kTileH); }
 
-static int stream_grid(uint64_t n, int sm_count);
 
 // Tree mode: chunks of at most P.rad_chunk samples; per chunk one persistent trace launch (as many
 // CTAs as fit on the device at once) and one in-order accumulate launch.

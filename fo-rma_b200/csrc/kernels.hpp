@@ -10,6 +10,8 @@ namespace forma {
 cudaError_t launch_render(const RenderParams& P, int sm_count, cudaStream_t stream, uint32_t* launches);
 // *d_mismatches += numerators in {0} U [2^-24, hi] for which div_const(n, b) != n / b
 cudaError_t launch_div_verify(float b, float hi, unsigned int* d_mismatches, int sm_count, cudaStream_t stream);
+// color_utils::srgb_encode (color_utils.rs:49-66) in place on nbytes of RGB8; lut = the u8 -> u8 map
+cudaError_t launch_srgb_encode(uint8_t* rgb, size_t nbytes, const uint8_t lut[256], int sm_count, cudaStream_t stream);
 cudaError_t launch_primary_hits(const PrimaryParams& P, cudaStream_t stream);
 cudaError_t launch_tonemap(const float4* sum, uint32_t spp, uint64_t begin, uint64_t end, uint8_t* rgb, int sm_count,
                            cudaStream_t stream);

@@ -133,4 +133,17 @@ std::vector<forma_rt_object> builtin_scene(int which) {
     return s;
 }
 
+// color_utils.rs:49-66: linear = (c / 255).clamp(0, 1); srgb = linear <= 0.0031308 ? 12.92 linear
+// : 1.055 linear^(1/2.4) - 0.055; (srgb * 255).round() as u8 - all in f32, round half away from zero.
+void srgb_encode_table(uint8_t table[256]) {
+    const float threshold = 0.0031308f, linear_scale = 12.92f, gamma = 1.0f / 2.4f, a = 1.055f, b = 0.055f;
+    for (int i = 0; i < 256; ++i) {
+        float linear = (float)i / 255.0f;
+        linear = linear < 0.0f ? 0.0f : (linear > 1.0f ? 1.0f : linear);
+        const float srgb = linear <= threshold ? linear * linear_scale : a * std::pow(linear, gamma) - b;
+        const float r = std::round(srgb * 255.0f);
+        table[i] = (uint8_t)(r < 0.0f ? 0.0f : (r > 255.0f ? 255.0f : r));
+    }
+}
+
 }  // namespace forma

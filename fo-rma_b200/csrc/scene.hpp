@@ -62,4 +62,7 @@ void quat_axes(const float q[4], V3& ax, V3& ay, V3& az);
 // tracer.rs:31-51: 00EQADWS key bits -> orbit delta
 V3 keys_to_delta(uint8_t keys, float delta_time);
 
+// color_utils::srgb_encode (color_utils.rs:49-66) for every u8 input: the function is a u8 -> u8 map
+void srgb_encode_table(uint8_t table[256]);
+
 }  // namespace forma

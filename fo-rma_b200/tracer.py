@@ -172,6 +172,23 @@ class TraceModel:
                                          lin.ctypes.data if lin is not None else None))
         return rgb, lin
 
+    def accumulate(self, spp_more: int, *, max_depth: int = MAX_DEPTH, want_linear=False):
+        """Progressive refinement: spp_more samples on top of the handle's running sum.
+        Returns (rgb of the average so far, linear_rgba | None, samples accumulated)."""
+        rgb = np.empty((self.height, self.width, 3), dtype=np.uint8)
+        lin = np.empty((self.height, self.width, 4), dtype=np.float32) if want_linear else None
+        n = ctypes.c_uint32(0)
+        check(_lib.lib().forma_rt_accumulate(self._h, spp_more, max_depth, rgb.ctypes.data,
+                                             lin.ctypes.data if lin is not None else None, ctypes.byref(n)))
+        return rgb, lin, n.value
+
+    def accumulate_reset(self):
+        check(_lib.lib().forma_rt_accumulate_reset(self._h))
+
+    def srgb_encode_device(self, d_rgb: int, nbytes: int, stream: int = 0):
+        """color_utils::srgb_encode (color_utils.rs:49-66) in place on a device RGB8 buffer."""
+        check(_lib.lib().forma_rt_srgb_encode_device(self._h, d_rgb, nbytes, stream or None))
+
     def primary_hits(self):
         ids = np.empty((self.height, self.width), dtype=np.int32)
         ts = np.empty((self.height, self.width), dtype=np.float32)
@@ -224,6 +241,23 @@ def update(model: TraceModel, keys: int, delta_time: float) -> None:
     pixels = np.empty(model.width * model.height * CHANNEL_COUNT, dtype=np.uint8)
     check(_lib.lib().forma_rt_update(model._h, keys & 0xFF, float(delta_time), pixels.ctypes.data))
     model.pixels = pixels
+
+
+def update_progressive(model: TraceModel, keys: int, delta_time: float) -> int:
+    """tracer::update with progressive refinement (added mode): one more sample per call while the camera and
+    the scene stand still, a fresh 1-spp frame otherwise.  Returns the samples accumulated in model.pixels."""
+    pixels = np.empty(model.width * model.height * CHANNEL_COUNT, dtype=np.uint8)
+    n = ctypes.c_uint32(0)
+    check(_lib.lib().forma_rt_update_progressive(model._h, keys & 0xFF, float(delta_time), pixels.ctypes.data, ctypes.byref(n)))
+    model.pixels = pixels
+    return n.value
+
+
+def srgb_table() -> np.ndarray:
+    """color_utils::srgb_encode (color_utils.rs:49-66) as its u8 -> u8 table."""
+    t = np.zeros(256, dtype=np.uint8)
+    check(_lib.lib().forma_rt_srgb_table(t.ctypes.data))
+    return t
 
 
 def save_image(model: TraceModel, sample: int, path: str = "out/basic.png") -> None:

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FORMA_RT_ABI_VERSION 1
+#define FORMA_RT_ABI_VERSION 2
 
 /* error codes */
 #define FORMA_RT_OK 0
@@ -43,6 +43,7 @@ extern "C" {
 #define FORMA_RT_NO_JITTER 1u /* xi_u = xi_v = 0.5 instead of tracer.rs:66-67's two draws (added mode) */
 #define FORMA_RT_PINHOLE 2u   /* skip camera.rs:63-64's lens sample: offset = 0 (added mode) */
 #define FORMA_RT_HOST_ONLY 4u /* no device: scene/camera bookkeeping only; every render call fails with FORMA_RT_ECUDA */
+#define FORMA_RT_SRGB_OUT 8u  /* RGB8 outputs pass through color_utils::srgb_encode (color_utils.rs:49-66) on the GPU (added mode) */
 
 /* forma_rt_options.accel */
 #define FORMA_RT_ACCEL_AUTO 0u  /* brute-force scan below FORMA_RT_BVH_THRESHOLD spheres, LBVH above */
@@ -60,7 +61,7 @@ typedef struct forma_rt_options {
     uint32_t struct_size; /* = sizeof(forma_rt_options) */
     int32_t device;       /* CUDA device ordinal */
     uint64_t seed;        /* Philox key; the reference's thread_rng is OS-seeded (utility.rs:5) */
-    uint32_t flags;       /* FORMA_RT_NO_JITTER | FORMA_RT_PINHOLE | FORMA_RT_HOST_ONLY */
+    uint32_t flags;       /* FORMA_RT_NO_JITTER | FORMA_RT_PINHOLE | FORMA_RT_HOST_ONLY | FORMA_RT_SRGB_OUT */
     uint32_t accel;       /* FORMA_RT_ACCEL_* */
 } forma_rt_options;
 
@@ -142,6 +143,17 @@ FORMA_RT_API int forma_rt_camera_set(forma_rt* ctx, const forma_rt_camera* cam);
  * (render, tracer.rs:57-81) into rgb[width*height*3] (RGB8, row-major, row 0 = top).
  * Frame k of a handle uses sample index k so successive frames are decorrelated. */
 FORMA_RT_API int forma_rt_update(forma_rt* ctx, uint8_t keys, float delta_time, uint8_t* rgb);
+/* Progressive refinement (added mode).  The handle keeps a per-pixel f32 running sum.
+ * forma_rt_accumulate traces samples [n, n + spp_more) of every pixel ON TOP of the n accumulated so far and
+ * writes the average of all n + spp_more: the sum continues tracer.rs:170-175's chain, so k calls are
+ * bit-identical to one forma_rt_render of the total.  *spp_total (nullable) receives n + spp_more.
+ * forma_rt_update_progressive is tracer::update (keys, orbit) with that buffer: one more sample per frame
+ * while the camera and the scene stand still, a fresh start at sample 0 whenever either changed. */
+FORMA_RT_API int forma_rt_accumulate(forma_rt* ctx, uint32_t spp_more, uint32_t max_depth, uint8_t* rgb,
+                                    float* linear_rgba, uint32_t* spp_total);
+FORMA_RT_API int forma_rt_accumulate_reset(forma_rt* ctx);
+FORMA_RT_API int forma_rt_update_progressive(forma_rt* ctx, uint8_t keys, float delta_time, uint8_t* rgb,
+                                            uint32_t* spp_total);
 /* tracer::save_image's loops (tracer.rs:168-184) without the PNG write: spp samples per pixel,
  * sample indices sample_offset .. sample_offset+spp-1, paths up to max_depth scatters
  * (tracer.rs:10: 50).  rgb (nullable): width*height*3 sqrt-gamma bytes of sum/spp.
@@ -184,6 +196,10 @@ FORMA_RT_API int forma_rt_synchronize(forma_rt* ctx);
 
 /* ---- misc -------------------------------------------------------------------------------------- */
 FORMA_RT_API int forma_rt_stats_get(forma_rt* ctx, forma_rt_stats* out);
+/* color_utils::srgb_encode (color_utils.rs:49-66) in place on nbytes of device RGB8 (4-byte aligned);
+ * the function maps u8 -> u8, forma_rt_srgb_table returns that map (host, no device needed). */
+FORMA_RT_API int forma_rt_srgb_encode_device(forma_rt* ctx, void* d_rgb, size_t nbytes, void* stream);
+FORMA_RT_API int forma_rt_srgb_table(uint8_t table[256]);
 /* RGB8 -> PNG file (the `image` crate's role at tracer.rs:186) */
 FORMA_RT_API int forma_rt_write_png(const char* path, const uint8_t* rgb, uint32_t width, uint32_t height);
 

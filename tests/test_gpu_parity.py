@@ -197,3 +197,86 @@ def test_save_image_png(tmp_path):  # tracer.rs:160-187
     with pytest.raises(forma_b200.tracer.FormaError) as e:
         forma_b200.save_image(m, 1, str(tmp_path / "no_such_dir" / "basic.png"))
     assert e.value.code == _lib.EIO
+
+
+def test_statistical_mode_against_sequential_rng():
+    """SURVEY 8(c) protocol 2: the reference draws from thread_rng (OS-seeded), so beside the same-stream
+    bit-exact checks the GPU image (counter RNG) is compared with the oracle driven by an independent
+    SEQUENTIAL generator consumed in the reference's order (Q14).  Tolerance, stated: the per-pixel RMSE of
+    the RGB8 images must not exceed 1.5 x the noise floor = RMSE of two sequential-RNG oracle runs with
+    different seeds at the same spp, and PSNR must be >= 30 dB at 512 spp."""
+    w, h, spp = 96, 64, 512
+    objs, cam = ob.builtin_scene(2), ob.camera_new(w, h)  # metal fuzz .2 / 1.0, two dielectrics (scenes.rs:62-156)
+    m = forma_b200.create_model(w, h, seed=2024)
+    m.scene.load_builtin(2)
+    rgb_g, _ = m.render(spp, want_linear=True)
+    rgb_a, _, _ = ob.render(objs, cam, w, h, spp, seed=1, flags=ob.FLAG_SEQ_RNG, nthreads=NT)
+    rgb_b, _, _ = ob.render(objs, cam, w, h, spp, seed=2, flags=ob.FLAG_SEQ_RNG, nthreads=NT)
+
+    def rmse(x, y):
+        return float(np.sqrt(np.mean((x.astype(np.float64) - y.astype(np.float64)) ** 2)))
+
+    floor = rmse(rgb_a, rgb_b)
+    got = max(rmse(rgb_g, rgb_a), rmse(rgb_g, rgb_b))
+    psnr = 20.0 * np.log10(255.0 / got)
+    assert 0.0 < floor < 8.0, floor
+    assert got <= 1.5 * floor, (got, floor)
+    assert psnr >= 30.0, psnr
+    # and no bias: channel means agree to a fraction of a grey level
+    assert np.abs(rgb_g.mean(axis=(0, 1)) - 0.5 * (rgb_a.mean(axis=(0, 1)) + rgb_b.mean(axis=(0, 1)))).max() < 0.6
+
+
+def test_progressive_accumulation_is_one_render():
+    """k calls of accumulate() continue tracer.rs:170-175's sum, so they are bit-identical to one
+    render of the total - on the scan path and on the tree path - and update_progressive() restarts exactly
+    when the camera or the scene changed."""
+    for which, w, h in ((2, 96, 64), (None, 80, 48)):
+        m = forma_b200.create_model(w, h, seed=31)
+        if which is None:
+            txt, objs, cam = load_scene_pair("scene_01", w, h)  # 363 primitives: LBVH, render_tree_kernel
+            m.scene.load_json(txt); m.scene.camera.use_json()
+        else:
+            m.scene.load_builtin(which)
+            objs, cam = ob.builtin_scene(which), ob.camera_new(w, h)
+        for k, more in enumerate((1, 3, 4)):
+            rgb_p, lin_p, n = m.accumulate(more, want_linear=True)
+        assert n == 8 and (lin_p[..., 3] == 8).all()
+        rgb_o, lin_o, _ = ob.render(objs, cam, w, h, 8, seed=31, nthreads=NT)
+        assert np.array_equal(bits(lin_p[..., :3]), bits(lin_o)) and np.array_equal(rgb_p, rgb_o)
+        m.accumulate_reset()
+        rgb_1, _, n = m.accumulate(2)
+        assert n == 2 and np.array_equal(rgb_1, ob.render(objs, cam, w, h, 2, seed=31, nthreads=NT)[0])
+    # the interactive loop: still camera -> refinement, a key -> fresh frame
+    w, h = 96, 64
+    m = forma_b200.create_model(w, h, seed=8)
+    cam = ob.camera_new(w, h)
+    ob.update_camera(cam, 0, 0.1)  # the first update() teleports the eye (Q12)
+    counts = [forma_b200.update_progressive(m, 0, 0.1) for _ in range(3)]
+    assert counts == [1, 2, 3]
+    assert np.array_equal(m.pixels.reshape(h, w, 3), ob.render(ob.builtin_scene(0), cam, w, h, 3, seed=8, nthreads=NT)[0])
+    assert forma_b200.update_progressive(m, 0b000100, 0.1) == 1  # 'A': the camera moved
+    ob.update_camera(cam, 0b000100, 0.1)
+    assert np.array_equal(m.pixels.reshape(h, w, 3), ob.render(ob.builtin_scene(0), cam, w, h, 1, seed=8, nthreads=NT)[0])
+    m.scene.objects[0].rotate((-1.0, 0.0, 0.0))  # the scene changed
+    assert forma_b200.update_progressive(m, 0, 0.1) == 1
+
+
+def test_srgb_encode_on_device():
+    """SURVEY 8(f-2): color_utils::srgb_encode as a GPU pass over RGB8, standalone and as an output flag."""
+    import torch
+    t = forma_b200.srgb_table()
+    w, h = 100, 37  # 11100 bytes: a multiple of 4; the odd-length tail is exercised below
+    m = forma_b200.create_model(w, h, seed=4)
+    m.scene.load_builtin(2)
+    rgb, _ = m.render(4)
+    ms = forma_b200.create_model(w, h, seed=4, flags=_lib.SRGB_OUT)
+    ms.scene.load_builtin(2)
+    rgb_s, _ = ms.render(4)
+    assert np.array_equal(rgb_s, t[rgb]) and not np.array_equal(rgb_s, rgb)
+    for n in (1, 2, 3, 255, 4096 + 3, 1 << 20):
+        x = torch.randint(0, 256, (n,), dtype=torch.uint8, device="cuda")
+        want = t[x.cpu().numpy()]
+        m.srgb_encode_device(x.data_ptr(), n)
+        m.synchronize()
+        torch.cuda.synchronize()
+        assert np.array_equal(x.cpu().numpy(), want)

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     L = _lib.lib()
     for name in declared:
         assert hasattr(L, name), name
-    assert L.forma_rt_abi_version() == 1
+    assert L.forma_rt_abi_version() == 2
 
 
 def test_no_cpu_fallback_render_fails_loudly_without_device():
@@ -136,3 +136,16 @@ def test_write_png_roundtrip(tmp_path):
     assert np.array_equal(np.asarray(Image.open(p).convert("RGB")), rgb)
     rc = _lib.lib().forma_rt_write_png(str(tmp_path / "missing_dir" / "a.png").encode(), rgb.ctypes.data, 53, 37)
     assert rc == _lib.EIO  # the reference panics when ./out is missing (tracer.rs:186)
+
+
+def test_srgb_encode_table_matches_color_utils():
+    """color_utils::srgb_encode (color_utils.rs:49-66) is a u8 -> u8 map; the library's table against an f64
+    evaluation of the same formula.  The f32 evaluation errs by < 5e-5 grey levels (a few ulp of a value <= 1, x 255)
+    and no entry sits within 2e-4 of a rounding boundary, so the last-ulp freedom of an f32 powf (Rust's, glibc's)
+    cannot move any of them."""
+    t = forma_b200.srgb_table()
+    lin = np.arange(256, dtype=np.float64) / 255.0
+    srgb = np.where(lin <= 0.0031308, lin * 12.92, 1.055 * lin ** (1.0 / 2.4) - 0.055) * 255.0
+    assert np.abs(srgb - np.floor(srgb) - 0.5).min() > 2e-4
+    assert np.array_equal(t, np.floor(srgb + 0.5).astype(np.uint8))
+    assert t[0] == 0 and t[255] == 255 and (np.diff(t.astype(int)) >= 0).all()
