@@ -69,6 +69,7 @@ SYMBOLS = {
     "forma_rt_camera_get": (_int, [_vp, ctypes.POINTER(Camera)]),
     "forma_rt_camera_set": (_int, [_vp, ctypes.POINTER(Camera)]),
     "forma_rt_update": (_int, [_vp, ctypes.c_uint8, ctypes.c_float, _vp]),
+    "forma_rt_set_partition": (_int, [_vp, _u32, _u32]),
     "forma_rt_accumulate": (_int, [_vp, _u32, _u32, _vp, _vp, ctypes.POINTER(_u32)]),
     "forma_rt_accumulate_reset": (_int, [_vp]),
     "forma_rt_update_progressive": (_int, [_vp, ctypes.c_uint8, ctypes.c_float, _vp, ctypes.POINTER(_u32)]),

@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <numeric>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -73,6 +74,7 @@ struct forma_rt {
     // render_tree_kernel tuning (FORMA_RT_REFILL / FORMA_RT_LEAF_BATCH override; not part of the ABI)
     uint32_t refill = 20;     // lanes idle before a warp stops walking to refill them
     uint32_t leaf_batch = 8;  // lanes that must stop progressing before the warp looks at its waiting leaves
+    uint32_t part_mod = 1, part_rem = 0;  // forma_rt_set_partition: this handle renders the 32x4 tiles t with t % part_mod == part_rem
     int fast_div = -1;   // div_const (trace.cuh): -1 not checked yet, 0 IEEE division, 1 verified multiply form
     uint32_t frame = 0;  // update() call counter -> sample index of the interactive frame
 
@@ -558,6 +560,9 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
     P.rk.expand(c->seed);
     P.rgb = d_rgb; P.sum = d_sum; P.rays = c->d_rays;
     P.prior = d_prior; P.spp_prior = d_prior ? spp_prior : 0;
+    P.part_mod = c->part_mod; P.part_rem = c->part_rem;
+    P.part_pitch = (c->width + 31) / 32;  // smallest pitch >= tiles per row that is coprime with part_mod
+    while (std::gcd(P.part_pitch, P.part_mod) != 1u) ++P.part_pitch;
     if (P.scene.bvh_nodes) {  // tree mode: rad holds a chunk of samples of the frame, <= kRadBudget bytes
         const size_t npix = (size_t)c->width * c->height;
         size_t chunk = kRadBudget / (npix * sizeof(float4));
@@ -595,7 +600,16 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
         ++launches;
     }
     c->stats.gpu_launches = launches;
-    c->stats.paths = (uint64_t)c->width * c->height * spp;
+    uint64_t own_pixels = (uint64_t)c->width * c->height;
+    if (c->part_mod > 1) {  // pixels of the 32x4 tiles this handle owns
+        own_pixels = 0;
+        const uint32_t tx = (c->width + 31) / 32, ty = (c->height + 3) / 4;
+        for (uint32_t y = 0; y < ty; ++y)
+            for (uint32_t x = 0; x < tx; ++x)
+                if ((y * P.part_pitch + x) % c->part_mod == c->part_rem)
+                    own_pixels += (uint64_t)std::min(32u, c->width - x * 32) * std::min(4u, c->height - y * 4);
+    }
+    c->stats.paths = own_pixels * spp;
     c->stats_pending = true;  // ray counter + kernel time are read back by whoever synchronises
     return FORMA_RT_OK;
 }
@@ -643,6 +657,14 @@ int forma_rt_update(forma_rt* ctx, uint8_t keys, float delta_time, uint8_t* rgb)
     int rc = render_to_host(ctx, 1, ctx->frame, 50, ctx->flags, rgb, nullptr);  // tracer.rs:54, MAX_DEPTH :10
     if (rc == FORMA_RT_OK) ctx->frame++;
     return rc;
+}
+
+int forma_rt_set_partition(forma_rt* ctx, uint32_t rank, uint32_t world) {
+    NEED_CTX(ctx);
+    if (world == 0 || rank >= world) return fail(FORMA_RT_EINVAL, "forma_rt_set_partition: need rank < world");
+    ctx->part_mod = world; ctx->part_rem = rank;
+    ctx->prog_spp = 0;  // a running sum belongs to one partition
+    return FORMA_RT_OK;
 }
 
 int forma_rt_accumulate_reset(forma_rt* ctx) {

@@ -82,6 +82,9 @@ struct RenderParams {
     unsigned long long* rays;  // device counter
     const float4* prior;       // nullable: per-pixel f32 sum of the spp_prior samples traced by earlier calls (progressive mode)
     uint32_t spp_prior;        // the new samples continue that sum; the write-out averages over spp_prior + spp
+    // tile-interleaved multi-GPU split: this launch owns the 32x4 tiles (tx, ty) with (ty * part_pitch + tx) % part_mod == part_rem;
+    // part_pitch >= tiles per row is coprime with part_mod, so the deal rotates from row to row
+    uint32_t part_mod, part_rem, part_pitch;
     float inv_w, inv_h;        // RN(1 / width), RN(1 / height)
     uint32_t fast_div;         // 1: div_const's multiply form was verified exhaustively for both divisors
     // ---- tree mode only (render_tree_kernel + accumulate_kernel, kernels.cu) ----

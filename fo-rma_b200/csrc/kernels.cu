@@ -66,6 +66,7 @@ __device__ __forceinline__ void write_out(const RenderParams& P, float3 col, uin
 #endif
 template <int MODE>
 __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(const __grid_constant__ RenderParams P) {
+    if ((blockIdx.y * P.part_pitch + blockIdx.x) % P.part_mod != P.part_rem) return;  // another GPU's tile
     const float4 *sph, *tri;
     stage_scene<MODE>(P.scene, sph, tri);
 
@@ -202,9 +203,12 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
     const float4 *sph = S.spheres, *tri = S.tris;
     const int lane = threadIdx.x & 31;
     constexpr unsigned kFull = 0xffffffffu;
-    const uint32_t tiles_x = (P.width + 7) / 8, tiles_y = (P.height + 3) / 4;
+    // this launch owns the 32x4 tiles t = j * part_mod + part_rem of a part_pitch-wide tile grid (the scan kernel's
+    // CTA tiles; columns >= ctas_x are padding); each is four 8x4 warp tiles
+    const uint32_t ctas_x = (P.width + kTileW - 1) / kTileW, ctas = P.part_pitch * ((P.height + kTileH - 1) / kTileH);
+    const uint32_t own = ctas > P.part_rem ? (ctas - P.part_rem + P.part_mod - 1) / P.part_mod : 0u;
     const uint32_t groups = (P.chunk_k + kBatchSamples - 1) / kBatchSamples;
-    const uint32_t n_batches = tiles_x * tiles_y * groups;  // < 2^32: checked by the launcher
+    const uint32_t n_batches = own * 4u * groups;  // < 2^32: checked by the launcher
     uint32_t batch_next = 0, batch_jobs = 0, batch_x = 0, batch_y = 0, batch_k0 = 0;  // warp-uniform
     const float fw = (float)P.width, fh = (float)P.height;
     const bool no_jitter = P.flags & FORMA_RT_NO_JITTER, pinhole = P.flags & FORMA_RT_PINHOLE;
@@ -270,11 +274,12 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
                 if (lane == 0) b = atomicAdd(P.job_counter, 1u);
                 b = __shfl_sync(kFull, b, 0);
                 if (b >= n_batches) { if (want) lane_done = true; break; }
-                const uint32_t tile = b / groups, grp = b % groups;
-                batch_x = (tile % tiles_x) * 8u; batch_y = (tile / tiles_x) * 4u;
+                const uint32_t sub = b / groups, grp = b % groups, t = (sub >> 2) * P.part_mod + P.part_rem;
+                batch_x = (t % P.part_pitch) * kTileW + (sub & 3u) * 8u; batch_y = (t / P.part_pitch) * kTileH;
                 batch_k0 = grp * kBatchSamples;
-                batch_jobs = min((uint32_t)kBatchSamples, P.chunk_k - batch_k0) * 32u;
+                batch_jobs = batch_x < P.width ? min((uint32_t)kBatchSamples, P.chunk_k - batch_k0) * 32u : 0u;  // padding column
                 batch_next = 0;
+                if (batch_jobs == 0u) continue;
             }
             const uint32_t job = batch_next + __popc(need & ((1u << lane) - 1u));
             batch_next = min(batch_next + (uint32_t)__popc(need), batch_jobs);
@@ -363,6 +368,10 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
 __global__ void accumulate_kernel(const __grid_constant__ RenderParams P, int first, int last) {
     const size_t npix = (size_t)P.width * P.height;
     for (size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x; p < npix; p += (size_t)gridDim.x * blockDim.x) {
+        if (P.part_mod > 1u) {  // another GPU's tile: leave its pixels alone
+            const uint32_t x = (uint32_t)(p % P.width), y = (uint32_t)(p / P.width);
+            if (((y / kTileH) * P.part_pitch + x / kTileW) % P.part_mod != P.part_rem) continue;
+        }
         float3 col = f3(0.0f, 0.0f, 0.0f);
         if (!first) { const float4 c = P.acc[p]; col = f3(c.x, c.y, c.z); }
         else if (P.prior) col = xyz(P.prior[p]);

@@ -6,6 +6,10 @@ with no data-path collective until the frame is assembled:
   sample-split   rank g traces samples sample_range(g) of every pixel into an f32 float4 sum buffer;
                  the exchange adds the buffers in rank order and tone-maps (tracer.rs:177-184).
 
+  tile-split     rank g traces every sample of the 32x4-pixel tiles t with t % world == g
+                 (forma_rt_set_partition) and stores RGB8 straight into rank 0's frame through a peer
+                 pointer: no exchange kernel at all, and bit-exact against one GPU (same sample order).
+
 The reference's only notion of parallelism is render_mt's 4 row bands (tracer.rs:83-134).
 """
 from __future__ import annotations
@@ -21,6 +25,30 @@ def sample_range(rank: int, world: int, spp_total: int) -> tuple[int, int]:
 def pixel_stripe(rank: int, world: int, npix: int) -> tuple[int, int]:
     """[begin, end) of the pixels `rank` reduces and tone-maps in the fused exchange."""
     return npix * rank // world, npix * (rank + 1) // world
+
+
+TILE_W, TILE_H = 32, 4  # the partition unit of forma_rt_set_partition (= render_kernel's CTA tile)
+
+
+def tile_pitch(width: int, world: int) -> int:
+    """Smallest pitch >= tiles per row that is coprime with `world`: the deal rotates from row to row."""
+    import math
+    p = (width + TILE_W - 1) // TILE_W
+    while math.gcd(p, world) != 1:
+        p += 1
+    return p
+
+
+def tile_owner(x: int, y: int, width: int, world: int) -> int:
+    """Rank that traces pixel (x, y) under the tile-interleaved split."""
+    return ((y // TILE_H) * tile_pitch(width, world) + x // TILE_W) % world
+
+
+def owner_map(width: int, height: int, world: int):
+    """[height, width] array of owning ranks (numpy; test and tooling aid)."""
+    import numpy as np
+    ys, xs = np.mgrid[0:height, 0:width]
+    return ((ys // TILE_H) * tile_pitch(width, world) + xs // TILE_W) % world
 
 
 def gather_bytes(dist, payload: bytes, device) -> list[bytes]:
@@ -63,3 +91,29 @@ class FusedExchange:
                                 self.rgb0, None, stream)
         self.dist.barrier()  # rank 0's frame is complete
         return 2
+
+
+class TileExchange:
+    """Tile-interleaved split over peer memory: rank 0 exports its RGB8 frame through CUDA IPC, every rank
+    renders its own tiles (all samples) straight into it.  One trace launch per rank and frame, no reduce."""
+
+    mode = "tile-interleaved (32x4 tiles), RGB8 stored into rank 0's frame over NVLink (CUDA IPC)"
+
+    def __init__(self, model, dist, device):
+        import ctypes
+        from . import _lib
+        self.m, self.dist = model, dist
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.npix = model.width * model.height
+        q = ctypes.c_void_p()
+        _lib.check(_lib.lib().forma_rt_device_alloc(model._h, self.npix * 3, ctypes.byref(q)))
+        self.rgb = q.value
+        handles = gather_bytes(dist, model.ipc_export(self.rgb), device)
+        self.rgb0 = self.rgb if self.rank == 0 else model.ipc_open(handles[0])
+        model.set_partition(self.rank, self.world)
+
+    def frame(self, spp: int, max_depth: int, stream: int) -> int:
+        self.m.render_device(spp, 0, max_depth, self.rgb0, None, stream)
+        self.dist.barrier()  # stream-ordered (NCCL on the launch stream): rank 0's frame is complete
+        return 1
+

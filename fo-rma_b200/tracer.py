@@ -182,6 +182,10 @@ class TraceModel:
                                              lin.ctypes.data if lin is not None else None, ctypes.byref(n)))
         return rgb, lin, n.value
 
+    def set_partition(self, rank: int, world: int):
+        """Tile-interleaved multi-GPU split: render only the 32x4 tiles t with t % world == rank."""
+        check(_lib.lib().forma_rt_set_partition(self._h, rank, world))
+
     def accumulate_reset(self):
         check(_lib.lib().forma_rt_accumulate_reset(self._h))
 

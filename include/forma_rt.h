@@ -168,6 +168,14 @@ FORMA_RT_API int forma_rt_save_image(forma_rt* ctx, uint32_t sample, const char*
  * closest hit or -1; t[width*height] = its distance (FLT_MAX on a miss). */
 FORMA_RT_API int forma_rt_primary_hits(forma_rt* ctx, int32_t* prim_id, float* t);
 
+/* Tile-interleaved multi-GPU split: after forma_rt_set_partition(rank, world) every render call of
+ * this handle traces only the 32x4-pixel tiles (tx, ty) with (ty * pitch + tx) % world == rank - pitch = the smallest
+ * integer >= tiles per row that is coprime with world, so the deal rotates from row to row - and leaves the
+ * other pixels of its output buffers untouched, so `world` handles - one per GPU - can write one frame (each
+ * rank stores straight into rank 0's buffer through a peer pointer).  Every pixel is traced by exactly one rank
+ * with the same sample order: bit-exact against a single GPU.  (0, 1) restores the whole frame. */
+FORMA_RT_API int forma_rt_set_partition(forma_rt* ctx, uint32_t rank, uint32_t world);
+
 /* ---- device-resident entry points (one process per GPU; torch.distributed moves the buffers) --- */
 /* Same as forma_rt_render but the outputs are DEVICE pointers on ctx's device and nothing is copied
  * to the host; runs on `stream` (a cudaStream_t, NULL = the handle's own stream) without

@@ -68,3 +68,19 @@ def test_partitions_cover_exactly():
             assert all(r[g][0] + r[g][1] == r[g + 1][0] for g in range(world - 1))
         s = [fd.pixel_stripe(g, world, 1920 * 1080) for g in range(world)]
         assert s[0][0] == 0 and s[-1][1] == 1920 * 1080 and all(s[g][1] == s[g + 1][0] for g in range(world - 1))
+
+
+def test_tile_interleave_covers_every_pixel_once():
+    """forma_rt_set_partition's ownership rule (32x4 tiles dealt round-robin): a partition of the frame,
+    balanced to within one tile, for ragged sizes too."""
+    from forma_b200 import distributed as fd
+    for w, h in ((1920, 1080), (600, 600), (67, 45), (31, 3), (1, 1)):
+        for world in (1, 2, 3, 4, 8):
+            own = fd.owner_map(w, h, world)
+            assert own.shape == (h, w) and own.min() >= 0 and own.max() < world
+            assert own[0, 0] == fd.tile_owner(0, 0, w, world) and own[h - 1, w - 1] == fd.tile_owner(w - 1, h - 1, w, world)
+            counts = np.bincount(own.ravel(), minlength=world)
+            assert counts.sum() == w * h
+            tiles = ((w + 31) // 32) * ((h + 3) // 4)
+            if tiles >= world:
+                assert counts.max() - counts.min() <= 2 * 32 * 4
