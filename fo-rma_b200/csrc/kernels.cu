@@ -106,15 +106,14 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
             while (s < P.spp) {
                 rng.sample = P.sample_offset + s;
                 const Rand4 r = rng.block(0, blk);
-                float px, py;
-                bool ok;
-                if (blk == 0) {
-                    xu = no_jitter ? 0.5f : r.x; xv = no_jitter ? 0.5f : r.y;
-                    px = 2.0f * r.z - 1.0f; py = 2.0f * r.w - 1.0f;
-                    ok = pinhole || !(px * px + py * py >= 1.0f);
-                } else {
-                    ok = lens_retry(r, px, py);
-                }
+                // block 0 = (xi_u, xi_v, lens try 0); a retry block = two lens tries (x, y), (z, w) (utility.rs:4-13).
+                // Both readings share the (z, w) try, so one branch-free evaluation serves fresh and retrying lanes.
+                const bool retry = blk != 0u;
+                const float ax = 2.0f * r.x - 1.0f, ay = 2.0f * r.y - 1.0f, bx = 2.0f * r.z - 1.0f, by = 2.0f * r.w - 1.0f;
+                const bool use_a = retry && !(ax * ax + ay * ay >= 1.0f);
+                const bool ok = use_a || pinhole || !(bx * bx + by * by >= 1.0f);
+                const float px = use_a ? ax : bx, py = use_a ? ay : by;
+                if (!retry) { xu = no_jitter ? 0.5f : r.x; xv = no_jitter ? 0.5f : r.y; }
                 if (ok) {
                     const float u = div_const(fx + xu, fw, P.inv_w, fast_div);  // tracer.rs:171
                     const float v = div_const(fy + xv, fh, P.inv_h, fast_div);  // tracer.rs:172
