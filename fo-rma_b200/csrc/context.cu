@@ -257,7 +257,15 @@ int upload_scene(forma_rt* c) {
             bin.n_spheres = NS; bin.n_tris = NT; bin.big_spheres = big_s; bin.big_tris = big_t;
             bin.n_bvh_spheres = NS - big_s; bin.count = (NS - big_s) + (NT - big_t);
             const float cl[3] = {clo.x, clo.y, clo.z}, ch[3] = {chi.x, chi.y, chi.z};
-            for (int k = 0; k < 3; ++k) { bin.cmin[k] = cl[k]; bin.cscale[k] = ch[k] > cl[k] ? 1024.0f / (ch[k] - cl[k]) : 0.0f; }
+            // one scale for all three axes: cubic Morton cells, so the tree splits a flat scene along its long axes
+            // first instead of spending every third level on the thin one
+            const float cext = std::max({ch[0] - cl[0], ch[1] - cl[1], ch[2] - cl[2]});
+            const bool iso = !std::getenv("FORMA_RT_MORTON_ANISO");
+            for (int k = 0; k < 3; ++k) {
+                bin.cmin[k] = cl[k];
+                const float e = iso ? cext : ch[k] - cl[k];
+                bin.cscale[k] = e > 0.0f ? 1024.0f / e : 0.0f;
+            }
             bc[0] = 0.5f * (ulo.x + uhi.x); bc[1] = 0.5f * (ulo.y + uhi.y); bc[2] = 0.5f * (ulo.z + uhi.z);
             const V3 half{0.5f * (uhi.x - ulo.x), 0.5f * (uhi.y - ulo.y), 0.5f * (uhi.z - ulo.z)};
             br2 = 1.0001f * dot(half, half);
