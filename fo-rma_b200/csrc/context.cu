@@ -187,7 +187,7 @@ int upload_scene(forma_rt* c) {
         return fail(FORMA_RT_EINVAL, "LBVH needs all spheres and triangles in one plane-free run of Scene.objects; use FORMA_RT_ACCEL_BRUTE");
     LbvhInput bin{};
     bool use_bvh = false;
-    float bc[3] = {0, 0, 0}, br2 = 0.0f, beps = 0.0f;
+    float bc[3] = {0, 0, 0}, br2 = 0.0f, beps = 0.0f, qstep[3] = {0, 0, 0}, bq = 0.0f;
     if (want_bvh && runs == 1 && ns + nt >= 2) {
         const int NS = (int)ns, NT = (int)nt, N = NS + NT;
         std::vector<V3> lo(N), hi(N);
@@ -271,6 +271,17 @@ int upload_scene(forma_rt* c) {
             br2 = 1.0001f * dot(half, half);
             const float scale = std::max({std::fabs(ulo.x), std::fabs(ulo.y), std::fabs(ulo.z), std::fabs(uhi.x), std::fabs(uhi.y), std::fabs(uhi.z)});
             beps = std::ldexp(scale, -16) + 1e-30f;
+            // the 16-bit grid the node boxes are stored on: 65533 cells over the tree's box plus one spare cell on
+            // either side (lbvh.cu rounds outwards by a whole extra cell); a flat axis gets a token extent
+            const float ul[3] = {ulo.x, ulo.y, ulo.z}, uh[3] = {uhi.x, uhi.y, uhi.z};
+            for (int k = 0; k < 3; ++k) {
+                const float ext = std::max({(uh[k] - ul[k]) * 1.0001f, scale * 1e-6f, 1e-20f});
+                qstep[k] = ext / 65533.0f;
+                bin.qmin[k] = ul[k] - qstep[k];
+                bin.qinv[k] = 1.0f / qstep[k];
+            }
+            bq = 0.0f;  // max 1/r over the spheres of the tree (the outsized ones were moved to the front)
+            for (int i = big_s; i < NS; ++i) bq = std::max(bq, 1.0f / spheres[i].w);
             use_bvh = true;
         }
     }
@@ -333,7 +344,8 @@ int upload_scene(forma_rt* c) {
         for (size_t k = 0; k < segments.size(); ++k)
             if (segments[k].sph_end > segments[k].sph_begin || segments[k].tri_end > segments[k].tri_begin) v.tree_seg = (int)k;
         v.bvh_center[0] = bc[0]; v.bvh_center[1] = bc[1]; v.bvh_center[2] = bc[2];
-        v.bvh_r2 = br2; v.bvh_eps = beps;
+        v.bvh_r2 = br2; v.bvh_eps = beps; v.bvh_q = bq;
+        for (int k = 0; k < 3; ++k) { v.bvh_qmin[k] = bin.qmin[k]; v.bvh_qstep[k] = qstep[k]; }
         c->stats.bvh_nodes = (uint32_t)(bin.count - 1);
         c->stats.accel_in_use = FORMA_RT_ACCEL_LBVH;
     }

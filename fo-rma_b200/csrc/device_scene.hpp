@@ -45,7 +45,7 @@ struct SceneView {
     const int* kindmat;
     const int* ids;
     // LBVH over spheres[0 .. n_spheres) (nullptr = brute force)
-    const float4* bvh_nodes;   // 4 float4 per internal node: see lbvh.cu
+    const uint4* bvh_nodes;    // 2 uint4 (32 B) per internal node: quantised child boxes + child codes, see lbvh.cu
     const int* bvh_prim;       // unified primitive index (< n_spheres: sphere) of sorted leaf l
     int big_spheres, big_tris; // with a tree: the first big_* packed primitives are scanned linearly
     int finite_materials;      // 1: every colour component of every list entry is finite (see black_path)
@@ -53,6 +53,9 @@ struct SceneView {
     float bvh_center[3];       // bounding sphere of everything the tree indexes
     float bvh_r2;              // its radius squared
     float bvh_eps;             // absolute box pad: 2^-16 x scene scale
+    float bvh_qmin[3];         // the tree's 16-bit grid: plane q on axis k lies at bvh_qmin[k] + q * bvh_qstep[k]
+    float bvh_qstep[3];
+    float bvh_q;               // max 1/radius over the spheres of the tree (0 without spheres): scales the sphere pad
     float cull_center[3];      // bounding sphere of every finite sphere and triangle (closest_hit's cull);
     float cull_r2;             // radius squared; +inf = never cull
     int n_segments;

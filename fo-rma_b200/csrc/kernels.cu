@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
     Winner w;
     Walk W;
     h.t = 0.0f; h.p = o; h.n = o; h.closest = FLT_MAX; h.obj = -1;
-    W.ix = W.iy = W.iz = W.ox = W.oy = W.oz = W.coef = 0.0f; W.node = kWalkDone; W.sp = 0;
+    W.g = RayGrid{}; W.node = kWalkDone; W.sp = 0;
 
     for (;;) {
         // ---- A. shade the rays whose walk has finished

@@ -3,14 +3,15 @@
 // (shapes/aabb.rs is a stub; tracer.rs:195-200 scans every object), so this only has to return what
 // the scan returns; see trace.cuh `bvh_closest` for how the walk stays exact.
 //
-// Node record (4 x float4 = 64 B per internal node k, children L and R):
-//   [4k+0] = (Lmin.x, Lmin.y, Lmin.z, Lmax.x)
-//   [4k+1] = (Lmax.y, Lmax.z, Rmin.x, Rmin.y)
-//   [4k+2] = (Rmin.z, Rmax.x, Rmax.y, Rmax.z)
-//   [4k+3] = (bits(L), bits(R), qL, qR)   child >= 0: internal node; child < 0: ~(unified primitive index)
-// q = max over the child's subtree of 1/radius (0 for triangles): the walk pads a box by
-// coef(ray) * q + eps so that the f32 sphere test of sphere.rs:23-51 can never report a hit that the
-// box test culled (DESIGN.md "LBVH").  prim[l] = primitive of sorted leaf l is kept for tooling only.
+// Node record (2 x uint4 = 32 B per internal node k, children L and R), read with one 256-bit load:
+//   w0 = Llo.x | Llo.y << 16   w1 = Llo.z | Lhi.x << 16   w2 = Lhi.y | Lhi.z << 16
+//   w3 = Rlo.x | Rlo.y << 16   w4 = Rlo.z | Rhi.x << 16   w5 = Rhi.y | Rhi.z << 16
+//   w6 = code(L)  w7 = code(R)          code >= 0: internal node; code < 0: ~(unified primitive index)
+// Box planes are u16 on a grid over the tree's bounding box (qmin + q / qinv per axis), lo rounded DOWN and
+// hi rounded UP by a whole extra cell, so a stored box always contains the f32 box: the walk (trace.cuh)
+// stays conservative and pads every box by coef(ray) * q_tree + eps so that the f32 sphere test of
+// sphere.rs:23-51 can never report a hit that the box test culled.  prim[l] = primitive of sorted leaf l is
+// kept for tooling only.
 #include <cfloat>
 #include <cstdint>
 
@@ -125,7 +126,7 @@ __device__ __forceinline__ int leaf_to_prim(const LbvhInput& in, int i) {  // le
 __global__ void refit_kernel(LbvhInput in, int n, const int2* __restrict__ children, const int* __restrict__ parent,
                              const float4* __restrict__ leaf_lo, const float4* __restrict__ leaf_hi,
                              const int* __restrict__ sorted_leaf, float4* node_lo, float4* node_hi,
-                             unsigned int* __restrict__ flags, float4* __restrict__ nodes) {
+                             unsigned int* __restrict__ flags, uint4* __restrict__ nodes) {
     const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
     if (leaf >= n) return;
     int node = parent[(n - 1) + leaf];
@@ -136,12 +137,15 @@ __global__ void refit_kernel(LbvhInput in, int n, const int2* __restrict__ child
         const int2 ch = children[node];
         const Box L = child_box(ch.x, leaf_lo, leaf_hi, sorted_leaf, node_lo, node_hi);
         const Box R = child_box(ch.y, leaf_lo, leaf_hi, sorted_leaf, node_lo, node_hi);
-        nodes[4 * node + 0] = make_float4(L.lo.x, L.lo.y, L.lo.z, L.hi.x);
-        nodes[4 * node + 1] = make_float4(L.hi.y, L.hi.z, R.lo.x, R.lo.y);
-        nodes[4 * node + 2] = make_float4(R.lo.z, R.hi.x, R.hi.y, R.hi.z);
         const int cl = ch.x < 0 ? ~leaf_to_prim(in, sorted_leaf[~ch.x]) : ch.x;
         const int cr = ch.y < 0 ? ~leaf_to_prim(in, sorted_leaf[~ch.y]) : ch.y;
-        nodes[4 * node + 3] = make_float4(__int_as_float(cl), __int_as_float(cr), L.q, R.q);
+        // (v - qmin) * qinv errs by < 0.02 cells (65535 x a few ulp), so floor - 1 / ceil + 1 are safely outside
+        auto qlo = [&](float v, int k) { return (uint32_t)fminf(fmaxf(floorf((v - in.qmin[k]) * in.qinv[k]) - 1.0f, 0.0f), 65535.0f); };
+        auto qhi = [&](float v, int k) { return (uint32_t)fminf(fmaxf(ceilf((v - in.qmin[k]) * in.qinv[k]) + 1.0f, 0.0f), 65535.0f); };
+        nodes[2 * node + 0] = make_uint4(qlo(L.lo.x, 0) | qlo(L.lo.y, 1) << 16, qlo(L.lo.z, 2) | qhi(L.hi.x, 0) << 16,
+                                         qhi(L.hi.y, 1) | qhi(L.hi.z, 2) << 16, qlo(R.lo.x, 0) | qlo(R.lo.y, 1) << 16);
+        nodes[2 * node + 1] = make_uint4(qlo(R.lo.z, 2) | qhi(R.hi.x, 0) << 16, qhi(R.hi.y, 1) | qhi(R.hi.z, 2) << 16,
+                                         (uint32_t)cl, (uint32_t)cr);
         __stcg(node_lo + node, make_float4(fminf(L.lo.x, R.lo.x), fminf(L.lo.y, R.lo.y), fminf(L.lo.z, R.lo.z), fmaxf(L.q, R.q)));
         __stcg(node_hi + node, make_float4(fmaxf(L.hi.x, R.hi.x), fmaxf(L.hi.y, R.hi.y), fmaxf(L.hi.z, R.hi.z), 0.0f));
         node = parent[node];
@@ -170,7 +174,7 @@ cudaError_t LbvhDevice::build(const LbvhInput& in, cudaStream_t stream) {
 
     if (n > capacity) {  // persistent outputs
         release();
-        cudaError_t e = cudaMalloc((void**)&nodes, sizeof(float4) * 4 * (size_t)(n - 1));
+        cudaError_t e = cudaMalloc((void**)&nodes, sizeof(uint4) * 2 * (size_t)(n - 1));
         if (e == cudaSuccess) e = cudaMalloc((void**)&prim, sizeof(int) * (size_t)n);
         if (e != cudaSuccess) { release(); return e; }
         capacity = n;

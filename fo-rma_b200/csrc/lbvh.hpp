@@ -17,10 +17,12 @@ struct LbvhInput {
     int count;              // primitives in the tree: n_bvh_spheres + (n_tris - big_tris)
     float cmin[3];          // centroid bounds -> 10-bit Morton grid: cell = (c - cmin) * cscale
     float cscale[3];
+    float qmin[3];          // the 16-bit grid the node boxes are stored on: plane = qmin + q / qinv
+    float qinv[3];
 };
 
 struct LbvhDevice {
-    float4* nodes = nullptr;  // 4 float4 per internal node (layout in lbvh.cu)
+    uint4* nodes = nullptr;   // 2 uint4 per internal node (layout in lbvh.cu)
     int* prim = nullptr;      // unified primitive index of sorted leaf l
     int n_leaves = 0;
     int capacity = 0;

@@ -266,15 +266,69 @@ __device__ __forceinline__ bool scene_culled(const SceneView& S, float3 o, float
     return a * (cc - S.cull_r2) - b * b > 1.52587890625e-05f * (a * (cc + S.cull_r2));
 }
 
-// One 64-byte node record as two 256-bit loads (LDG.E.256, sm_100+): a warp's lanes sit at different
-// nodes, so every load instruction costs one L1 tag look-up per lane - two per node instead of four.
-__device__ __forceinline__ void load_node(const float4* __restrict__ nodes, int node, float4& n0, float4& n1,
-                                          float4& n2, float4& n3) {
-    const float4* p = nodes + 4 * (size_t)node;
-    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=f"(n0.x), "=f"(n0.y), "=f"(n0.z), "=f"(n0.w), "=f"(n1.x), "=f"(n1.y), "=f"(n1.z), "=f"(n1.w) : "l"(p));
-    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=f"(n2.x), "=f"(n2.y), "=f"(n2.z), "=f"(n2.w), "=f"(n3.x), "=f"(n3.y), "=f"(n3.z), "=f"(n3.w) : "l"(p + 2));
+// One 32-byte node record as ONE 256-bit load (LDG.E.256, sm_100+): a warp's lanes sit at different nodes,
+// so every load instruction costs one L1 look-up per lane, and the walk is bound by exactly those requests
+// (profiles/r01o_render_tree_kernel_D_ncu.md).  Layout (lbvh.cu): six words of u16 box planes on the tree's
+// 16-bit grid - (Llo.x | Llo.y << 16), (Llo.z | Lhi.x << 16), (Lhi.y | Lhi.z << 16), the same for R - and the
+// two child codes.
+struct QNode {
+    uint32_t w0, w1, w2, w3, w4, w5;
+    int cL, cR;
+};
+__device__ __forceinline__ QNode load_node(const uint4* __restrict__ nodes, int node) {
+    QNode n;
+    const uint4* p = nodes + 2 * (size_t)node;
+    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(n.w0), "=r"(n.w1), "=r"(n.w2), "=r"(n.w3), "=r"(n.w4), "=r"(n.w5), "=r"(n.cL), "=r"(n.cR) : "l"(p));
+    return n;
+}
+
+// A ray's view of the tree's grid.  A box plane q (grid units) on axis k lies at qmin_k + q step_k; padded by
+// `pad` towards the outside its ray parameter is
+//     t = (qmin_k -+ pad + q step_k - o_k) / d_k = q * A_k + B(lo|hi)_k,   A_k = step_k / d_k,
+//     Blo_k = (qmin_k - pad - o_k) / d_k,  Bhi_k = (qmin_k + pad - o_k) / d_k
+// - one FFMA per plane straight from the 16-bit value.  Exactness: a child box is visited iff the ray's
+// interval through the PADDED box reaches [0, closest]; pad = coef(ray) * q_tree + eps with
+// coef = 2^-19 (|o - C|^2 + R^2), q_tree = max 1/r over the spheres of the tree: it exceeds the largest miss
+// distance at which the f32 test of sphere.rs:25-29 can still report disc > 0 (|disc error| <= 25 eps_f32 a L^2,
+// L <= |o - C| + R), and eps = 2^-16 x scene scale covers the triangle test's rounding and that of the two
+// roundings in q * A + B (each <= 1 ulp of |o_k / d_k| in t, i.e. <= 2^-23 |o_k| in space).  The grid itself is
+// conservative by construction (lbvh.cu rounds lo down and hi up by a whole extra cell).  So no primitive the
+// scan would accept is culled, and the tie rule makes the visiting order irrelevant.
+struct RayGrid {
+    float ax, ay, az;        // A_k
+    float blx, bly, blz;     // Blo_k
+    float bhx, bhy, bhz;     // Bhi_k
+};
+__device__ __forceinline__ RayGrid ray_grid(const SceneView& S, float3 o, float3 d) {
+    const float huge = 1e30f;
+    const float ix = fabsf(d.x) < 1e-30f ? copysignf(huge, d.x) : 1.0f / d.x;
+    const float iy = fabsf(d.y) < 1e-30f ? copysignf(huge, d.y) : 1.0f / d.y;
+    const float iz = fabsf(d.z) < 1e-30f ? copysignf(huge, d.z) : 1.0f / d.z;
+    const float3 oc = o - f3(S.bvh_center);
+    const float pad = __fmaf_rn(1.9073486e-6f * (dot(oc, oc) + S.bvh_r2), S.bvh_q, S.bvh_eps);  // 2^-19 (...) q + eps
+    RayGrid g;
+    g.ax = S.bvh_qstep[0] * ix; g.ay = S.bvh_qstep[1] * iy; g.az = S.bvh_qstep[2] * iz;
+    g.blx = (S.bvh_qmin[0] - pad - o.x) * ix; g.bhx = (S.bvh_qmin[0] + pad - o.x) * ix;
+    g.bly = (S.bvh_qmin[1] - pad - o.y) * iy; g.bhy = (S.bvh_qmin[1] + pad - o.y) * iy;
+    g.blz = (S.bvh_qmin[2] - pad - o.z) * iz; g.bhz = (S.bvh_qmin[2] + pad - o.z) * iz;
+    return g;
+}
+// [near, far] of the ray through both padded child boxes of a node, clipped to [0, closest]
+__device__ __forceinline__ void slab_pair(const QNode& n, const RayGrid& g, float closest, float& nearL, float& farL,
+                                          float& nearR, float& farR) {
+    float t0 = __fmaf_rn((float)(n.w0 & 0xffffu), g.ax, g.blx), t1 = __fmaf_rn((float)(n.w1 >> 16), g.ax, g.bhx);
+    nearL = fminf(t0, t1); farL = fmaxf(t0, t1);
+    t0 = __fmaf_rn((float)(n.w0 >> 16), g.ay, g.bly); t1 = __fmaf_rn((float)(n.w2 & 0xffffu), g.ay, g.bhy);
+    nearL = fmaxf(nearL, fminf(t0, t1)); farL = fminf(farL, fmaxf(t0, t1));
+    t0 = __fmaf_rn((float)(n.w1 & 0xffffu), g.az, g.blz); t1 = __fmaf_rn((float)(n.w2 >> 16), g.az, g.bhz);
+    nearL = fmaxf(fmaxf(nearL, fminf(t0, t1)), 0.0f); farL = fminf(fminf(farL, fmaxf(t0, t1)), closest);
+    t0 = __fmaf_rn((float)(n.w3 & 0xffffu), g.ax, g.blx); t1 = __fmaf_rn((float)(n.w4 >> 16), g.ax, g.bhx);
+    nearR = fminf(t0, t1); farR = fmaxf(t0, t1);
+    t0 = __fmaf_rn((float)(n.w3 >> 16), g.ay, g.bly); t1 = __fmaf_rn((float)(n.w5 & 0xffffu), g.ay, g.bhy);
+    nearR = fmaxf(nearR, fminf(t0, t1)); farR = fminf(farR, fmaxf(t0, t1));
+    t0 = __fmaf_rn((float)(n.w4 & 0xffffu), g.az, g.blz); t1 = __fmaf_rn((float)(n.w5 >> 16), g.az, g.bhz);
+    nearR = fmaxf(fmaxf(nearR, fminf(t0, t1)), 0.0f); farR = fminf(fminf(farR, fmaxf(t0, t1)), closest);
 }
 
 // Primary-beam cull, once per pixel.  Every primary ray of pixel (x, y) is (1 - tau) o + tau F, tau >= 0,
@@ -314,47 +368,20 @@ __device__ __forceinline__ bool beam_culled(const forma_rt_camera& c, const Scen
     return Cq > 0.0 && A > 0.0 && (B >= 0.0 || B * B < A * Cq);
 }
 
-// LBVH walk over the primitives the tree indexes (lbvh.cu).  Exactness: a child box is visited iff
-// the ray's interval through the PADDED box reaches [0, closest]; the pad
-//     coef(ray) * q(child) + eps,   coef = 2^-19 (|o - C|^2 + R^2),  q = max 1/r below the child
-// exceeds the largest miss distance at which the f32 test of sphere.rs:25-29 can still report
-// disc > 0 (|disc error| <= 25 eps_f32 a L^2, L <= |o - C| + R), and eps = 2^-16 x scene scale covers
-// the triangle test's and the slab test's own rounding.  So no primitive the scan would accept is
-// culled, and the tie rule makes the visiting order irrelevant.
+// LBVH walk over the primitives the tree indexes (lbvh.cu), one ray to completion (primary_hits_kernel).
 __device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __restrict__ sph,
                                             const float4* __restrict__ tri, float3 o, float3 d, float a,
                                             HitState& h, Winner& w) {
-    const float huge = 1e30f;
-    const float ix = fabsf(d.x) < 1e-30f ? copysignf(huge, d.x) : 1.0f / d.x;
-    const float iy = fabsf(d.y) < 1e-30f ? copysignf(huge, d.y) : 1.0f / d.y;
-    const float iz = fabsf(d.z) < 1e-30f ? copysignf(huge, d.z) : 1.0f / d.z;
-    const float ox = -o.x * ix, oy = -o.y * iy, oz = -o.z * iz;
-    const float3 oc = o - f3(S.bvh_center);
-    const float coef = 1.9073486e-6f * (dot(oc, oc) + S.bvh_r2);  // 2^-19
-    const float eps = S.bvh_eps;
-
+    const RayGrid g = ray_grid(S, o, d);
     int stack[64];
     int sp = 0;
     int node = 0;
     for (;;) {
-        float4 n0, n1, n2, n3;
-        load_node(S.bvh_nodes, node, n0, n1, n2, n3);
-        const float padL = __fmaf_rn(coef, n3.z, eps), padR = __fmaf_rn(coef, n3.w, eps);
-        // slab test, (b - o) / d as fma(b, 1/d, -o/d); explicit fma: this part need not match the oracle
-        float t0 = __fmaf_rn(n0.x - padL, ix, ox), t1 = __fmaf_rn(n0.w + padL, ix, ox);
-        float nearL = fminf(t0, t1), farL = fmaxf(t0, t1);
-        t0 = __fmaf_rn(n0.y - padL, iy, oy); t1 = __fmaf_rn(n1.x + padL, iy, oy);
-        nearL = fmaxf(nearL, fminf(t0, t1)); farL = fminf(farL, fmaxf(t0, t1));
-        t0 = __fmaf_rn(n0.z - padL, iz, oz); t1 = __fmaf_rn(n1.y + padL, iz, oz);
-        nearL = fmaxf(fmaxf(nearL, fminf(t0, t1)), 0.0f); farL = fminf(fminf(farL, fmaxf(t0, t1)), h.closest);
-        t0 = __fmaf_rn(n1.z - padR, ix, ox); t1 = __fmaf_rn(n2.y + padR, ix, ox);
-        float nearR = fminf(t0, t1), farR = fmaxf(t0, t1);
-        t0 = __fmaf_rn(n1.w - padR, iy, oy); t1 = __fmaf_rn(n2.z + padR, iy, oy);
-        nearR = fmaxf(nearR, fminf(t0, t1)); farR = fminf(farR, fmaxf(t0, t1));
-        t0 = __fmaf_rn(n2.x - padR, iz, oz); t1 = __fmaf_rn(n2.w + padR, iz, oz);
-        nearR = fmaxf(fmaxf(nearR, fminf(t0, t1)), 0.0f); farR = fminf(fminf(farR, fmaxf(t0, t1)), h.closest);
+        const QNode n = load_node(S.bvh_nodes, node);
+        float nearL, farL, nearR, farR;
+        slab_pair(n, g, h.closest, nearL, farL, nearR, farR);
         const bool hitL = nearL <= farL, hitR = nearR <= farR;
-        int cL = __float_as_int(n3.x), cR = __float_as_int(n3.y);
+        int cL = n.cL, cR = n.cR;
         int next = -1;   // internal node to descend into
         bool have = false;
         if (hitL && hitR) {
@@ -385,20 +412,13 @@ constexpr int kWalkDone = (int)0x80000000;  // never a leaf code: leaves are ~l 
 constexpr int kWalkPop = (int)0x80000001;   // convergent walk: this lane takes its next node from the stack
 
 struct Walk {
-    float ix, iy, iz, ox, oy, oz;  // 1/d and -o/d
-    float coef;                    // 2^-19 (|o - C|^2 + R^2): the pad scale of this ray
-    int node;                      // >= 0 internal, < 0 leaf ~node, kWalkDone
+    RayGrid g;
+    int node;  // >= 0 internal, < 0 leaf ~node, kWalkDone, kWalkPop
     int sp;
 };
 
 __device__ __forceinline__ void walk_begin(const SceneView& S, float3 o, float3 d, Walk& W) {
-    const float huge = 1e30f;
-    W.ix = fabsf(d.x) < 1e-30f ? copysignf(huge, d.x) : 1.0f / d.x;
-    W.iy = fabsf(d.y) < 1e-30f ? copysignf(huge, d.y) : 1.0f / d.y;
-    W.iz = fabsf(d.z) < 1e-30f ? copysignf(huge, d.z) : 1.0f / d.z;
-    W.ox = -o.x * W.ix; W.oy = -o.y * W.iy; W.oz = -o.z * W.iz;
-    const float3 oc = o - f3(S.bvh_center);
-    W.coef = 1.9073486e-6f * (dot(oc, oc) + S.bvh_r2);  // 2^-19
+    W.g = ray_grid(S, o, d);
     W.node = 0;
     W.sp = 0;
 }
@@ -420,25 +440,11 @@ struct WalkStack {
 // One internal node: test both child boxes, descend into the nearer hit child (pushing the other), or ask
 // for the next stack entry (kWalkPop, taken by the caller's next iteration).
 __device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, const WalkStack& stack, float closest) {
-    const int node = W.node;
-    const float eps = S.bvh_eps;
-    float4 n0, n1, n2, n3;
-    load_node(S.bvh_nodes, node, n0, n1, n2, n3);
-    const float padL = __fmaf_rn(W.coef, n3.z, eps), padR = __fmaf_rn(W.coef, n3.w, eps);
-    float t0 = __fmaf_rn(n0.x - padL, W.ix, W.ox), t1 = __fmaf_rn(n0.w + padL, W.ix, W.ox);
-    float nearL = fminf(t0, t1), farL = fmaxf(t0, t1);
-    t0 = __fmaf_rn(n0.y - padL, W.iy, W.oy); t1 = __fmaf_rn(n1.x + padL, W.iy, W.oy);
-    nearL = fmaxf(nearL, fminf(t0, t1)); farL = fminf(farL, fmaxf(t0, t1));
-    t0 = __fmaf_rn(n0.z - padL, W.iz, W.oz); t1 = __fmaf_rn(n1.y + padL, W.iz, W.oz);
-    nearL = fmaxf(fmaxf(nearL, fminf(t0, t1)), 0.0f); farL = fminf(fminf(farL, fmaxf(t0, t1)), closest);
-    t0 = __fmaf_rn(n1.z - padR, W.ix, W.ox); t1 = __fmaf_rn(n2.y + padR, W.ix, W.ox);
-    float nearR = fminf(t0, t1), farR = fmaxf(t0, t1);
-    t0 = __fmaf_rn(n1.w - padR, W.iy, W.oy); t1 = __fmaf_rn(n2.z + padR, W.iy, W.oy);
-    nearR = fmaxf(nearR, fminf(t0, t1)); farR = fminf(farR, fmaxf(t0, t1));
-    t0 = __fmaf_rn(n2.x - padR, W.iz, W.oz); t1 = __fmaf_rn(n2.w + padR, W.iz, W.oz);
-    nearR = fmaxf(fmaxf(nearR, fminf(t0, t1)), 0.0f); farR = fminf(fminf(farR, fmaxf(t0, t1)), closest);
+    const QNode n = load_node(S.bvh_nodes, W.node);
+    float nearL, farL, nearR, farR;
+    slab_pair(n, W.g, closest, nearL, farL, nearR, farR);
     const bool hitL = nearL <= farL, hitR = nearR <= farR;
-    const int cL = __float_as_int(n3.x), cR = __float_as_int(n3.y);
+    const int cL = n.cL, cR = n.cR;
     if (hitL && hitR) {
         const bool swap = nearR < nearL;  // descend into the nearer child, push the other
         W.node = swap ? cR : cL;
