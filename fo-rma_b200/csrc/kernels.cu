@@ -105,18 +105,23 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
             float xu = 0.0f, xv = 0.0f;
             while (s < P.spp) {
                 rng.sample = P.sample_offset + s;
-                const Rand4 r = rng.block(0, blk);
+                const float4 k = rng.block_k(0, blk);  // xi = k * 2^-24 exactly, so 2 xi - 1 = RN(k 2^-23 - 1) and x + xi = RN(k 2^-24 + x): one FFMA each
                 // block 0 = (xi_u, xi_v, lens try 0); a retry block = two lens tries (x, y), (z, w) (utility.rs:4-13).
                 // Both readings share the (z, w) try, so one branch-free evaluation serves fresh and retrying lanes.
                 const bool retry = blk != 0u;
-                const float ax = 2.0f * r.x - 1.0f, ay = 2.0f * r.y - 1.0f, bx = 2.0f * r.z - 1.0f, by = 2.0f * r.w - 1.0f;
+                const float s23 = 1.0f / 8388608.0f, s24 = 1.0f / 16777216.0f;
+                const float ax = __fmaf_rn(k.x, s23, -1.0f), ay = __fmaf_rn(k.y, s23, -1.0f);
+                const float bx = __fmaf_rn(k.z, s23, -1.0f), by = __fmaf_rn(k.w, s23, -1.0f);
                 const bool use_a = retry && !(ax * ax + ay * ay >= 1.0f);
                 const bool ok = use_a || pinhole || !(bx * bx + by * by >= 1.0f);
                 const float px = use_a ? ax : bx, py = use_a ? ay : by;
-                if (!retry) { xu = no_jitter ? 0.5f : r.x; xv = no_jitter ? 0.5f : r.y; }
+                if (!retry) {  // tracer.rs:171-172: x + xi_u, (height - y) + xi_v
+                    xu = no_jitter ? fx + 0.5f : __fmaf_rn(k.x, s24, fx);
+                    xv = no_jitter ? fy + 0.5f : __fmaf_rn(k.y, s24, fy);
+                }
                 if (ok) {
-                    const float u = div_const(fx + xu, fw, P.inv_w, fast_div);  // tracer.rs:171
-                    const float v = div_const(fy + xv, fh, P.inv_h, fast_div);  // tracer.rs:172
+                    const float u = div_const(xu, fw, P.inv_w, fast_div);  // tracer.rs:171
+                    const float v = div_const(xv, fh, P.inv_h, fast_div);  // tracer.rs:172
                     camera_ray_at(P.cam, px, py, u, v, pinhole, o, d);
                     col = col + sky(d);  // tracer.rs:174 with get_color = tracer.rs:213-217
                     ++s; blk = 0;

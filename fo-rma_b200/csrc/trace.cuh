@@ -36,7 +36,8 @@ struct Rand4 {
 // Round keys k + r*W are the same for every call of a launch, so the host expands them once
 // (RoundKeys, device_scene.hpp) and the kernel reads them as constant-bank operands: a round is
 // two IMAD.WIDE (hi and lo of each product in one instruction) and two 3-input LOP3.
-__device__ __forceinline__ Rand4 philox_unit4(const RoundKeys& rk, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) {
+// the ten rounds: four u32 words
+__device__ __forceinline__ uint4 philox_raw4(const RoundKeys& rk, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
         const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
@@ -45,12 +46,16 @@ __device__ __forceinline__ Rand4 philox_unit4(const RoundKeys& rk, uint32_t c0, 
         const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ rk.k[2 * r + 1];
         c1 = (uint32_t)p1; c3 = (uint32_t)p0; c0 = n0; c2 = n2;
     }
+    return make_uint4(c0, c1, c2, c3);
+}
+__device__ __forceinline__ Rand4 philox_unit4(const RoundKeys& rk, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) {
+    const uint4 c = philox_raw4(rk, c0, c1, c2, c3);
     const float s = 1.0f / 16777216.0f;
     Rand4 o;
-    o.x = (float)(c0 >> 8) * s;
-    o.y = (float)(c1 >> 8) * s;
-    o.z = (float)(c2 >> 8) * s;
-    o.w = (float)(c3 >> 8) * s;
+    o.x = (float)(c.x >> 8) * s;
+    o.y = (float)(c.y >> 8) * s;
+    o.z = (float)(c.z >> 8) * s;
+    o.w = (float)(c.w >> 8) * s;
     return o;
 }
 
@@ -59,6 +64,11 @@ struct PathRng {
     uint32_t pixel, sample;
     __device__ __forceinline__ Rand4 block(uint32_t slot, uint32_t blk) const {
         return philox_unit4(rk, pixel, sample, slot, blk);
+    }
+    // the same block as four 24-bit integers k (as floats): the unit float is k * 2^-24, exactly
+    __device__ __forceinline__ float4 block_k(uint32_t slot, uint32_t blk) const {
+        const uint4 c = philox_raw4(rk, pixel, sample, slot, blk);
+        return make_float4((float)(c.x >> 8), (float)(c.y >> 8), (float)(c.z >> 8), (float)(c.w >> 8));
     }
 };
 
