@@ -338,12 +338,12 @@ def emit(args, world, value, ms_per_step, rays_step, kern_ms, st, clocks, e2e, l
             "bound": "fp32-issue",  # neither HBM nor tensor: SURVEY §8(d); see DESIGN.md "Roofline"
             "achieved": round(achieved, 3) if achieved else None, "peak": round(fp32_peak, 2), "unit": "TFLOP/s",
             "frac": round(achieved / fp32_peak, 4) if achieved else None,
-            # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r01j_render_kernel_C_ncu.md):
+            # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (capture r02f, profiles/r01j_render_kernel_C_ncu.md):
             # the 6.22 MB frame is still in L2 when the kernel ends, the scene is 192 B
-            "traffic": 37376 if world == 1 else None,
-            "issue_slots": {"active_pct": 76.7, "warp_instr_per_path": 12.1, "source": "ncu smsp__issue_active / smsp__inst_executed of this kernel "
-                            "on this config, profiles/r01j_render_kernel_C_ncu.md: the kernel is issue-bound; 47 % of its instructions "
-                            "are the counter RNG + rejection sampling, which the flop model does not count"},
+            "traffic": 50688 if world == 1 else None,
+            "issue_slots": {"active_pct": 78.5, "warp_instr_per_path": 7.5, "source": "ncu smsp__issue_active / smsp__inst_executed of this kernel "
+                            "on this config (capture r02f, profiles/r01j_render_kernel_C_ncu.md): the kernel is issue-bound; 40 % of its "
+                            "instructions are the counter RNG + rejection sampling, which the flop model does not count"},
             "peak_source": f"{st.sm_count} SMs x 128 lanes x 2 x {sm_mhz:.0f} MHz (sm_max_mhz of MEASURED_PEAKS.json, {src}); "
                            "no FMA in the exact build, so its own ceiling is half of this",
             "kernel": "render_kernel", "kernel_ms": round(kern_ms, 4),
