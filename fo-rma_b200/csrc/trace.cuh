@@ -507,13 +507,18 @@ __device__ __forceinline__ bool scatter(const SceneView& S, const PathRng& rng, 
     const int kind = km & 0xff, material = km >> 8;
     const Rand4 r = rng.block(slot, 0);
     new_o = h.p;
+    const bool dielectric = material == 2 && kind == FORMA_RT_SPHERE;
+    // metal (sphere.rs:97, also at fuzz 0: Q7), lambertian and "light" all draw random_in_unit_sphere: ONE rejection
+    // loop for the lanes of all three, instead of one per material branch
+    float3 rs = f3(0.0f, 0.0f, 0.0f);
+    if (!dielectric) rs = random_in_unit_sphere(rng, slot, r);
     if (material == 1) {  // metal: sphere.rs:91-105 == plane.rs:108-122
         float fuzz = S.material[h.obj].w;
         float3 reflected = reflect(unit(d), h.n);
-        new_d = reflected + fuzz * random_in_unit_sphere(rng, slot, r);
+        new_d = reflected + fuzz * rs;
         return dot(new_d, h.n) > 0.0f;
     }
-    if (material == 2 && kind == FORMA_RT_SPHERE) {  // dielectric: sphere.rs:107-145 (spheres only, plane.rs:52-59)
+    if (dielectric) {  // sphere.rs:107-145 (spheres only, plane.rs:52-59)
         const float ref_idx = 1.3f;
         float3 outward_normal = f3(0.0f, 0.0f, 0.0f);
         float3 reflected = reflect(d, h.n);
@@ -535,7 +540,7 @@ __device__ __forceinline__ bool scatter(const SceneView& S, const PathRng& rng, 
         return true;
     }
     // lambertian (sphere.rs:84-89, plane.rs:101-106) and "light" (sphere.rs:147-152): same ray
-    float3 target = h.p + h.n + random_in_unit_sphere(rng, slot, r);
+    float3 target = h.p + h.n + rs;
     new_d = target - h.p;
     return true;
 }

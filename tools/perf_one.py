@@ -7,17 +7,20 @@ import forma_b200
 which = sys.argv[1]
 S = os.path.join(ROOT, "tests", "golden", "scenes")
 name, w, h, spp = {"A": ("scene_01", 600, 600, 50), "B": ("scene_05", 1920, 1080, 4), "C": ("scene_09", 1920, 1080, 256),
-                   "D": (None, 1920, 1080, 16)}[which]
+                   "D": (None, 1920, 1080, 16), "S0": ("builtin0", 1920, 1080, 64), "S2": ("builtin2", 1920, 1080, 64)}[which]
 if len(sys.argv) > 2: spp = int(sys.argv[2])
 m = forma_b200.create_model(w, h, seed=0)
-if name:
+if name and name.startswith("builtin"):
+    m.scene.load_builtin(int(name[-1]))
+    txt = None
+elif name:
     txt = open(os.path.join(S, name + ".json")).read()
 else:
     import importlib.util, json
     spec = importlib.util.spec_from_file_location("g", os.path.join(ROOT, "python-extras", "sphere_scene_generator.py"))
     mod = importlib.util.module_from_spec(spec); spec.loader.exec_module(mod)
     txt = json.dumps(mod.generate(100_000))
-m.scene.load_json(txt); m.scene.camera.use_json()
+if txt: m.scene.load_json(txt); m.scene.camera.use_json()
 for _ in range(2):
     m.render(spp)
     st = m.stats()
