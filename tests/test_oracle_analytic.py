@@ -216,3 +216,16 @@ def test_sequential_rng_mode_agrees_statistically():
     _, b, _ = ob.render(objs, cam, 24, 24, 64, seed=1, flags=ob.FLAG_SEQ_RNG)
     assert not np.array_equal(a, b)
     assert abs(float(a.mean() - b.mean())) / 64 < 0.02
+
+
+def test_oracle_output_pins():
+    """tests/golden/oracle_pins.json (tools/make_oracle_pins.py): the oracle's images, hit ids, hit distances and ray
+    counts on six fixed cases.  Not reference outputs - a guard against the oracle drifting under the GPU suite."""
+    import importlib.util, json, os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("pins", os.path.join(root, "tools", "make_oracle_pins.py"))
+    mod = importlib.util.module_from_spec(spec); spec.loader.exec_module(mod)
+    pins = json.load(open(os.path.join(root, "tests", "golden", "oracle_pins.json")))
+    assert len(pins) == len(mod.CASES)
+    for n, w, h, spp, seed in mod.CASES:
+        assert mod.run(n, w, h, spp, seed) == pins[f"{n} {w}x{h} {spp}spp seed{seed}"], n
