@@ -280,3 +280,40 @@ def test_srgb_encode_on_device():
         m.synchronize()
         torch.cuda.synchronize()
         assert np.array_equal(x.cpu().numpy(), want)
+
+
+def test_edge_cases_empty_tiny_and_degenerate():
+    """Empty list (every ray is sky), a 1x1 and a 1-row frame, a plane-only scene, and a tree over degenerate
+    geometry: coincident spheres (ties), a zero-radius sphere, zero-area triangles, a NaN sphere (stays on the
+    exact linear scan) - all bit-exact against the oracle on the scan and the LBVH path."""
+    empty = np.zeros(0, dtype=OBJECT_DTYPE)
+    for w, h, spp in ((1, 1, 5), (37, 1, 3), (64, 40, 2)):
+        m = forma_b200.create_model(w, h, seed=3)
+        m.scene.load_objects(empty)
+        assert_render_equal(m, empty, ob.camera_new(w, h), w, h, spp, 3)
+        ids, t = m.primary_hits()
+        assert (ids == -1).all() and (t == np.finfo(np.float32).max).all()
+    w, h = 72, 40
+    only_plane = np.stack([plane((0, 0, -2), (0, 0, -1), (1.5, 1.0, 5), mat=1, col=(.9, .6, .6), id=5)])
+    m = forma_b200.create_model(w, h, seed=4)
+    m.scene.load_objects(only_plane)
+    assert_render_equal(m, only_plane, ob.camera_new(w, h), w, h, 3, 4)
+    rng = np.random.default_rng(21)
+    objs = [sphere((0, 0, -3), 0.5, mat=0, col=(.8, .2, .2), id=i) for i in range(3)]             # coincident: lowest index wins
+    objs += [sphere((1, 0, -3), 0.0, mat=0, id=10), tri((0, 1, -3), (0, 1, -3), (0, 1, -3), id=11),  # zero radius / zero area
+             tri((-1, -1, -3), (1, 1, -3), (0, 0, -3), id=12),                                      # collinear
+             sphere((float("nan"), 0, -3), 0.5, mat=0, id=13)]                                      # NaN centre: never hit
+    for i in range(24):
+        c = rng.uniform(-2, 2, 3); c[2] -= 4
+        objs.append(sphere(c, rng.uniform(.1, .5), mat=int(rng.integers(0, 4)), col=rng.uniform(.1, .9, 3), fuzz=rng.uniform(0, 1), id=100 + i))
+    objs = np.stack(objs)
+    cam = ob.camera_new(w, h)
+    for accel in (_lib.ACCEL_BRUTE, _lib.ACCEL_LBVH):
+        m = forma_b200.create_model(w, h, seed=6, accel=accel)
+        m.scene.load_objects(objs)
+        assert_render_equal(m, objs, cam, w, h, 3, 6)
+        ids, t = m.primary_hits()
+        ids_o, t_o = ob.primary_hits(objs, cam, w, h)
+        assert np.array_equal(ids, ids_o) and np.array_equal(bits(t), bits(t_o))
+        assert 0 in ids and 1 not in ids and 2 not in ids and 13 not in ids
+    assert m.stats().accel_in_use == _lib.ACCEL_LBVH
