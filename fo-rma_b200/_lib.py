@@ -92,6 +92,28 @@ SYMBOLS = {
 }
 
 
+class FxStats(ctypes.Structure):
+    _fields_ = [("n_effects", ctypes.c_uint32), ("n_passes", ctypes.c_uint32), ("gpu_launches", ctypes.c_uint32),
+                ("kernel_ms", ctypes.c_float), ("total_ms", ctypes.c_float), ("bytes_moved", ctypes.c_uint64)]
+
+
+FX_UNFUSED = 1
+# name -> (restype, argtypes): the full surface of include/forma_fx.h (same library)
+SYMBOLS_FX = {
+    "forma_fx_create": (_int, [_int, _u32, _u32, _u32, ctypes.POINTER(_vp)]),
+    "forma_fx_destroy": (None, [_vp]),
+    "forma_fx_resize": (_int, [_vp, _u32, _u32]),
+    "forma_fx_update_effects": (_int, [_vp, _vp, _u32]),
+    "forma_fx_run": (_int, [_vp, _vp, _vp, ctypes.c_float]),
+    "forma_fx_run_device": (_int, [_vp, _vp, _vp, ctypes.c_float, _vp]),
+    "forma_fx_apply_device": (_int, [_vp, _int, _vp, _vp, ctypes.c_float, _vp]),
+    "forma_fx_run_traced": (_int, [_vp, _vp, _u32, _u32, _u32, ctypes.c_float, _vp, _vp]),
+    "forma_fx_effect_name": (ctypes.c_char_p, [_int]),
+    "forma_fx_synchronize": (_int, [_vp]),
+    "forma_fx_stats_get": (_int, [_vp, ctypes.POINTER(FxStats)]),
+}
+
+
 def build_library(verbose: bool = False) -> str:
     """Compile csrc/ for sm_100a into libforma_rt.so (nvcc cross-compiles without a GPU)."""
     cmd = ["make", "-C", os.path.join(_HERE, "csrc")]
@@ -110,7 +132,7 @@ def lib() -> ctypes.CDLL:
                 f"{LIB_PATH} is missing: build it with `make -C fo-rma_b200/csrc` or __graft_entry__.build(). "
                 "forma_b200 has no CPU fallback.")
         L = ctypes.CDLL(LIB_PATH)
-        for name, (res, args) in SYMBOLS.items():
+        for name, (res, args) in {**SYMBOLS, **SYMBOLS_FX}.items():
             fn = getattr(L, name)  # AttributeError here = header/library skew
             fn.restype, fn.argtypes = res, args
         if L.forma_rt_abi_version() != 2:

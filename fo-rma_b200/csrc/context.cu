@@ -17,6 +17,8 @@
 #include "kernels.hpp"
 #include "lbvh.hpp"
 #include "png.hpp"
+#include "postfx.hpp"
+#include "../../include/forma_fx.h"
 #include "scene.hpp"
 
 namespace {
@@ -60,6 +62,10 @@ constexpr uint32_t kBvhThreshold = 16;       // ACCEL_AUTO: LBVH at or above thi
 constexpr size_t kRadBudget = 1ull << 30;    // tree mode: bytes of per-path radiance kept between trace and accumulate
 
 }  // namespace
+
+namespace forma {
+int set_last_error(int code, const std::string& msg) { return fail(code, msg); }
+}  // namespace forma
 
 struct forma_rt {
     int device = 0;
@@ -677,6 +683,33 @@ int forma_rt_update(forma_rt* ctx, uint8_t keys, float delta_time, uint8_t* rgb)
     int rc = render_to_host(ctx, 1, ctx->frame, 50, ctx->flags, rgb, nullptr);  // tracer.rs:54, MAX_DEPTH :10
     if (rc == FORMA_RT_OK) ctx->frame++;
     return rc;
+}
+
+// include/forma_fx.h: trace, widen RGB8 -> RGBA8 and run the filter chain on the tracer's stream; one D2H at the end
+int forma_fx_run_traced(forma_fx* fx, forma_rt* ctx, uint32_t spp, uint32_t sample_offset, uint32_t max_depth,
+                        float time, uint8_t* rgb, uint8_t* dst_rgba) {
+    NEED_DEV(ctx);
+    if (!fx || !dst_rgba) return fail(FORMA_RT_EINVAL, "forma_fx_run_traced: null handle or frame");
+    if (forma::fx_device(fx) != ctx->device || forma::fx_width(fx) != ctx->width || forma::fx_height(fx) != ctx->height)
+        return fail(FORMA_RT_EINVAL, "forma_fx_run_traced: tracer and filter handles differ in device or frame size");
+    const size_t npix = (size_t)ctx->width * ctx->height;
+    CU_TRY(ctx->d_rgb.ensure(npix * 3));
+    cudaStream_t s = ctx->stream;
+    CU_TRY(cudaEventRecord(ctx->ev_begin, s));
+    int rc = render_on_device(ctx, spp, sample_offset, max_depth, ctx->flags, ctx->d_rgb.p, nullptr, s);
+    if (rc) return rc;
+    const uint8_t* d_out = nullptr;
+    if ((rc = forma::fx_run_from_rgb8(fx, ctx->d_rgb.p, time, s, &d_out))) return rc;
+    if (rgb) CU_TRY(cudaMemcpyAsync(rgb, ctx->d_rgb.p, npix * 3, cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaMemcpyAsync(dst_rgba, d_out, npix * 4, cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaMemcpyAsync(ctx->h_rays, ctx->d_rays, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaEventRecord(ctx->ev_end, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    ctx->stats.rays = *ctx->h_rays;
+    ctx->stats_pending = false;
+    CU_TRY(cudaEventElapsedTime(&ctx->stats.kernel_ms, ctx->ev_k0, ctx->ev_k1));
+    CU_TRY(cudaEventElapsedTime(&ctx->stats.total_ms, ctx->ev_begin, ctx->ev_end));
+    return FORMA_RT_OK;
 }
 
 int forma_rt_set_partition(forma_rt* ctx, uint32_t rank, uint32_t world) {

@@ -6,7 +6,7 @@ import collections, csv, glob, io, os, re, subprocess, sys, tempfile
 rep, kern = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-obj = os.path.join(ROOT, "fo-rma_b200", "csrc", "build", "kernels.cu.o")
+obj = os.path.join(ROOT, "fo-rma_b200", "csrc", "build", os.environ.get("NCU_LINES_OBJ", "kernels.cu.o"))
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", obj], cwd=tmp, capture_output=True)
 dis = subprocess.run(["nvdisasm", "-g", "-c", glob.glob(tmp + "/*.cubin")[0]], capture_output=True, text=True).stdout
