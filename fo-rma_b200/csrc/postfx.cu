@@ -249,7 +249,21 @@ __global__ void __launch_bounds__(kFxBlock, 4) fx_segment_kernel(const FxPass P)
             if (first == FORMA_FX_PIXELATE) {  // pixelate.comp.wgsl:16-22: x0 % 4 == 0, so the four share a block
                 const uint32_t v = __ldg(src + (size_t)(y & ~7u) * P.w + (x0 & ~7u));
                 t[u][0] = t[u][1] = t[u][2] = t[u][3] = v;
-            } else if (first == FORMA_FX_ANAGLYPH) {  // anaglyph.comp.wgsl:14-17: red from x - 10, blue from x + 10
+            } else if (first == FORMA_FX_ANAGLYPH && VEC) {
+                // anaglyph.comp.wgsl:14-17: red from x - 10, blue from x + 10.  x0 % 4 == 0 and w % 4 == 0, so the
+                // texels come as aligned pairs (x0 - 10, x0 - 9), (x0 - 8, x0 - 7), (x0 + 10, ..), (x0 + 12, ..), each
+                // pair wholly inside or wholly outside the row
+                const uint2* row2 = reinterpret_cast<const uint2*>(src + row);
+                const uint2 z = make_uint2(0u, 0u);
+                const uint2 r0 = x0 >= 12u ? __ldg(row2 + (x0 - 10u) / 2u) : z;
+                const uint2 r1 = x0 >= 8u ? __ldg(row2 + (x0 - 8u) / 2u) : z;
+                const uint2 b0 = x0 + 10u < P.w ? __ldg(row2 + (x0 + 10u) / 2u) : z;
+                const uint2 b1 = x0 + 12u < P.w ? __ldg(row2 + (x0 + 12u) / 2u) : z;
+                t[u][0] = (r0.x & 255u) | (b0.x & 0x00FF0000u) | 0xFF000000u;
+                t[u][1] = (r0.y & 255u) | (b0.y & 0x00FF0000u) | 0xFF000000u;
+                t[u][2] = (r1.x & 255u) | (b1.x & 0x00FF0000u) | 0xFF000000u;
+                t[u][3] = (r1.y & 255u) | (b1.y & 0x00FF0000u) | 0xFF000000u;
+            } else if (first == FORMA_FX_ANAGLYPH) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     const uint32_t x = x0 + i;
@@ -356,10 +370,10 @@ struct forma_fx {
     cudaEvent_t ev_begin = nullptr, ev_k0 = nullptr, ev_k1 = nullptr, ev_end = nullptr;
     std::vector<uint8_t> effects;
     // a pass = effects [first, first + count) in one launch; rd / wr: 0 input, 1 / 2 intermediates, 3 output
-    struct Pass { uint32_t first, count; int rd, wr; };
+    struct Pass { uint32_t first, count; int rd, wr; bool zero_rest; };
     std::vector<Pass> plan;
     bool fast_div = false;    // noise's divisions by 10 and 20 verified against IEEE division on this device
-    bool zero_first = false;  // flip_axis on a non-square frame: unwritten texels must read as the first frame's zeros
+    bool ragged_flip = false;  // flip_axis on a non-square frame: the chain runs unfused on the reference's wiring
     uint8_t *d_t1 = nullptr, *d_t2 = nullptr, *d_in = nullptr, *d_out = nullptr;
     float4* d_circles = nullptr;
     forma_fx_stats stats{};
@@ -409,15 +423,20 @@ void make_plan(forma_fx* f) {
     const uint32_t n = (uint32_t)f->effects.size();
     bool has_flip = false;
     for (uint8_t e : f->effects) has_flip |= e == FORMA_FX_FLIP_AXIS;
-    f->zero_first = has_flip && f->width != f->height;
-    if ((f->flags & FORMA_FX_UNFUSED) || f->zero_first) {
+    f->ragged_flip = has_flip && f->width != f->height;
+    if ((f->flags & FORMA_FX_UNFUSED) || f->ragged_flip) {
+        bool written[4] = {false, false, false, false};  // this run has filled the texture
         for (uint32_t i = 0; i < n; ++i) {
             int rd, wr;
             if (i == 0) { rd = 0; wr = n == 1 ? 3 : 1; }
             else if (i == n - 1) { wr = 3; rd = (i % 2 == 1) ? 1 : 2; }
             else if (i % 2 == 1) { rd = 1; wr = 2; }
             else { rd = 2; wr = 1; }
-            f->plan.push_back({i, 1, rd, wr});
+            // flip_axis on a non-square frame leaves texels unwritten.  They keep the texture's content: an earlier
+            // pass's output if this run has written the texture, else the zeros of the reference's first frame.
+            const bool zero_rest = f->ragged_flip && f->effects[i] == FORMA_FX_FLIP_AXIS && !written[wr];
+            written[wr] = true;
+            f->plan.push_back({i, 1, rd, wr, zero_rest});
         }
     } else {
         uint32_t i = 0;
@@ -425,7 +444,7 @@ void make_plan(forma_fx* f) {
             uint32_t cnt = 1;
             if (f->effects[i] != FORMA_FX_FLIP_AXIS)
                 while (i + cnt < n && cnt < kMaxOps && per_texel(f->effects[i + cnt])) ++cnt;
-            f->plan.push_back({i, cnt, 0, 0});
+            f->plan.push_back({i, cnt, 0, 0, false});
             i += cnt;
         }
         const size_t m = f->plan.size();
@@ -491,14 +510,14 @@ int run_chain(forma_fx* f, const uint8_t* d_src, uint8_t* d_dst, float time, cud
     const bool own = s == f->stream;
     if (own) FX_TRY(cudaEventRecord(f->ev_k0, s));
     uint32_t launches = 0;
-    if (f->zero_first) {
-        FX_TRY(cudaMemsetAsync(f->d_t1, 0, f->bytes(), s));
-        FX_TRY(cudaMemsetAsync(f->d_t2, 0, f->bytes(), s));
-        FX_TRY(cudaMemsetAsync(d_dst, 0, f->bytes(), s));
-    }
     for (const forma_fx::Pass& p : f->plan) {
         const uint8_t* rd = p.rd == 0 ? d_src : (p.rd == 1 ? f->d_t1 : f->d_t2);
         uint8_t* wr = p.wr == 3 ? d_dst : (p.wr == 1 ? f->d_t1 : f->d_t2);
+        if (p.zero_rest) {  // the texels outside the min(w, h) square, which flip_axis cannot reach
+            const size_t w = f->width, h = f->height;
+            if (w > h) FX_TRY(cudaMemset2DAsync(wr + h * 4, w * 4, 0, (w - h) * 4, h, s));
+            else FX_TRY(cudaMemsetAsync(wr + w * w * 4, 0, (h - w) * w * 4, s));
+        }
         if (int rc = launch_pass(f, f->effects.data() + p.first, p.count, rd, wr, time, s)) return rc;
         ++launches;
     }
