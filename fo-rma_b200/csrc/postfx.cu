@@ -63,7 +63,7 @@ __device__ __forceinline__ float chan(uint32_t t, int k, const float* lut) { ret
 
 // A filter maps packed texels to packed texels: it decodes only the channels it reads and encodes only the channels
 // it computes.  A channel it passes through keeps its byte, which is what textureStore(textureLoad(c)) gives for every
-// c (enc(c / 255) == c, tests/test_postfx_oracle.py); so two filters in a row need no conversion between them.
+// c (enc(c / 255) == c for all 256 values; checked in tests/); so two filters in a row need no conversion between them.
 __device__ __forceinline__ uint32_t gray_texel(uint32_t e, uint32_t t) { return __byte_perm(e, t, 0x7000); }  // e,e,e,t.a
 __device__ __forceinline__ uint32_t rgb1_texel(uint32_t er, uint32_t eg, uint32_t eb) {                       // r,g,b,255
     return __byte_perm(__byte_perm(er, eg, 0x0040), eb, 0x4410) | 0xFF000000u;
