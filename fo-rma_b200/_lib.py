@@ -1,4 +1,5 @@
-"""ctypes binding of libforma_rt.so — every symbol include/forma_rt.h declares, nothing else.
+"""ctypes binding of libforma_rt.so — every symbol include/forma_rt.h, forma_fx.h and forma_frag.h declare,
+nothing else.
 
 The library is built in-tree by fo-rma_b200/csrc/Makefile (`__graft_entry__.build()`); importing
 this module fails loudly when it is missing.  There is no CPU fallback anywhere in this package.
@@ -114,6 +115,31 @@ SYMBOLS_FX = {
 }
 
 
+class FragParams(ctypes.Structure):
+    _fields_ = [("time", ctypes.c_float), ("res_x", ctypes.c_float), ("res_y", ctypes.c_float),
+                ("aspect", ctypes.c_float), ("flags", ctypes.c_uint32)]
+
+
+class FragStats(ctypes.Structure):
+    _fields_ = [("rays", ctypes.c_uint64), ("gpu_launches", ctypes.c_uint32), ("kernel_ms", ctypes.c_float),
+                ("total_ms", ctypes.c_float)]
+
+
+FRAG_RT, FRAG_RT2 = 1, 2
+FRAG_SRGB_SURFACE = 1
+# name -> (restype, argtypes): the full surface of include/forma_frag.h (same library)
+SYMBOLS_FRAG = {
+    "forma_frag_create": (_int, [_int, _u32, _u32, ctypes.POINTER(_vp)]),
+    "forma_frag_destroy": (None, [_vp]),
+    "forma_frag_resize": (_int, [_vp, _u32, _u32]),
+    "forma_frag_render": (_int, [_vp, _int, ctypes.POINTER(FragParams), _vp, _vp]),
+    "forma_frag_render_device": (_int, [_vp, _int, ctypes.POINTER(FragParams), _vp, _vp, _vp]),
+    "forma_frag_light_direction": (_int, [ctypes.c_float, _vp]),
+    "forma_frag_synchronize": (_int, [_vp]),
+    "forma_frag_stats_get": (_int, [_vp, ctypes.POINTER(FragStats)]),
+}
+
+
 def build_library(verbose: bool = False) -> str:
     """Compile csrc/ for sm_100a into libforma_rt.so (nvcc cross-compiles without a GPU)."""
     cmd = ["make", "-C", os.path.join(_HERE, "csrc")]
@@ -132,7 +158,7 @@ def lib() -> ctypes.CDLL:
                 f"{LIB_PATH} is missing: build it with `make -C fo-rma_b200/csrc` or __graft_entry__.build(). "
                 "forma_b200 has no CPU fallback.")
         L = ctypes.CDLL(LIB_PATH)
-        for name, (res, args) in {**SYMBOLS, **SYMBOLS_FX}.items():
+        for name, (res, args) in {**SYMBOLS, **SYMBOLS_FX, **SYMBOLS_FRAG}.items():
             fn = getattr(L, name)  # AttributeError here = header/library skew
             fn.restype, fn.argtypes = res, args
         if L.forma_rt_abi_version() != 2:
