@@ -51,23 +51,40 @@ class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
-        self.rows, self.proc, self.index = [], None, index
+    def __init__(self, index, enabled=True):
+        self.rows, self.proc, self.index, self.enabled = [], None, index, enabled
 
-    def __enter__(self):
+    def start(self):
+        """Launch nvidia-smi and wait for its first row (it takes seconds to come up on an 8-GPU box, longer than a
+        short timed region); call before the last warm-up steps."""
+        if not self.enabled:
+            return self
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=lambda: self.rows.extend(self.proc.stdout), daemon=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            t0 = time.perf_counter()
+            while not self.rows and time.perf_counter() - t0 < 10.0:
+                time.sleep(0.01)
         except OSError:
             self.proc = None
         return self
 
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line)
+
+    def __enter__(self):
+        if self.enabled and self.proc is None:
+            self.start()
+        self.rows.clear()  # keep only the rows sampled inside the timed region
+        return self
+
     def __exit__(self, *a):
         if self.proc:
-            time.sleep(0.15)
+            time.sleep(0.05)
             self.proc.terminate()
             self.t.join(timeout=2)
 
@@ -198,6 +215,7 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    clk = ClockSampler(local, enabled=rank == 0).start()  # rank 0 samples its own GPU
     for _ in range(max(args.warmup, 3)):
         step()
     sync()
@@ -205,7 +223,7 @@ def run_ours(args):
     launches = 0
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     kernel_ms = []
-    with ClockSampler(local) as clk:
+    with clk:
         sync()
         t_wall = time.perf_counter()
         for a, b in ev:

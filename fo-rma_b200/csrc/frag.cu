@@ -120,63 +120,71 @@ struct FrameConst {
 namespace rt1 {
 constexpr float EPSILON = 4e-4f;  // rt.wgsl:7
 constexpr int SAMPLES = 1000;     // rt.wgsl:8
+constexpr int kGroupTail = 8;     // a warp with at most this many live paths finishes them on 4-lane groups
 
 // Hit (rt.wgsl:25-29); material = (color, f0), f0 < 0 = no hit
 struct Hit { float t; V3 normal; V3 color; float f0; };
 
-// rt.wgsl:77-85 `compare` after rt.wgsl:43-52 `intersect_plane` (Plane(0., vec3(0., 1., 0.), ...), rt.wgsl:94)
-__device__ __forceinline__ void plane(Hit& a, const Ray& r) {
+// The four primitive tests of a query are written without branches (selects on the accept condition): they are
+// independent of one another, and in one basic block the scheduler interleaves their dependent chains.  That is what
+// a lone long-running lane needs - its loop trip is a latency chain, not an issue-slot budget.
+
+// rt.wgsl:77-85 `compare` after rt.wgsl:43-52 `intersect_plane` (Plane(0., vec3(0., 1., 0.), ...), rt.wgsl:94):
+// true when `compare` would take the candidate, whose t is returned
+__device__ __forceinline__ bool plane_t(float at, const Ray& r, float& t) {
     const V3 n = v3(0.0f, 1.0f, 0.0f);
     const float dotnd = dot(n, r.direction);
-    if (dotnd > 0.0f) return;
-    const float t = -(dot(r.origin, n) + 0.0f) / dotnd;
-    if (t < a.t) { a.t = t; a.normal = n; a.color = v3(0.5f, 0.4f, 0.3f); a.f0 = 0.04f; }
+    t = -(dot(r.origin, n) + 0.0f) / dotnd;
+    return !(dotnd > 0.0f) && t < at;
 }
 
 // rt.wgsl:77-85 `compare` after rt.wgsl:54-73 `intersect_sphere`; every sphere has radius 1 (rt.wgsl:91-93)
-__device__ __forceinline__ void sphere(Hit& a, const Ray& r, V3 center, V3 color, float f0) {
+__device__ __forceinline__ bool sphere_t(float at, const Ray& r, V3 center, float& t) {
     const float radius = 1.0f;
     const V3 op = center - r.origin;
     const float b = dot(op, r.direction);
-    float det = b * b - dot(op, op) + radius * radius;
-    if (det < 0.0f) return;
-    det = sqrtf(det);
-    float t = b - det;
-    if (t < 0.0f) t = b + det;
-    if (t < 0.0f) return;
-    if (t < a.t) { a.t = t; a.normal = (r.origin + t * r.direction - center) / radius; a.color = color; a.f0 = f0; }
+    const float det = b * b - dot(op, op) + radius * radius;
+    // det < 0 is rejected below whatever sq is; 1 keeps sqrtf on its fast path there (a negative, zero or
+    // subnormal argument takes the slow one)
+    const float sq = sqrtf(det < 0.0f ? 1.0f : det);
+    const float t0 = b - sq;
+    t = t0 < 0.0f ? b + sq : t0;
+    return !(det < 0.0f) && !(t < 0.0f) && t < at;
+}
+
+// the winner's normal and material (rt.wgsl:91-94): centres differ only in x (-2, 0, 2 = 2 * which - 4), radius 1;
+// which: 0 plane, 1..3 spheres, < 0 no hit
+__device__ __forceinline__ Hit surface(int which, float t, const Ray& ray) {
+    Hit hit;
+    hit.t = t;
+    const V3 center = v3((float)(2 * which - 4), 1.0f, 0.0f);
+    const V3 ns = (ray.origin + t * ray.direction - center) / 1.0f;
+    hit.normal = which == 0 ? v3(0.0f, 1.0f, 0.0f) : ns;
+    hit.color = which == 0 ? v3(0.5f, 0.4f, 0.3f) : v3(which == 1 ? 1.0f : 0.0f, which == 2 ? 1.0f : 0.0f, which == 3 ? 1.0f : 0.0f);
+    hit.f0 = which == 0 ? 0.04f : which == 1 ? 0.04f : which == 2 ? 0.1f : 0.5f;
+    if (which < 0) { hit.normal = splat(0.0f); hit.color = splat(-1.0f); hit.f0 = -1.0f; }
+    return hit;
 }
 
 // rt.wgsl:88-102
 __device__ __forceinline__ Hit intersect_scene(const Ray& ray) {
-    Hit hit = {1e10f, splat(0.0f), splat(-1.0f), -1.0f};
-    plane(hit, ray);
-    sphere(hit, ray, v3(-2.0f, 1.0f, 0.0f), v3(1.0f, 0.0f, 0.0f), 0.04f);
-    sphere(hit, ray, v3(0.0f, 1.0f, 0.0f), v3(0.0f, 1.0f, 0.0f), 0.1f);
-    sphere(hit, ray, v3(2.0f, 1.0f, 0.0f), v3(0.0f, 0.0f, 1.0f), 0.5f);
-    return hit;
+    float best = 1e10f, t;
+    int which = -1;
+    if (plane_t(best, ray, t)) { best = t; which = 0; }
+    if (sphere_t(best, ray, v3(-2.0f, 1.0f, 0.0f), t)) { best = t; which = 1; }
+    if (sphere_t(best, ray, v3(0.0f, 1.0f, 0.0f), t)) { best = t; which = 2; }
+    if (sphere_t(best, ray, v3(2.0f, 1.0f, 0.0f), t)) { best = t; which = 3; }
+    return surface(which, best, ray);
 }
 
 // the shadow query of rt.wgsl:121-126 only asks whether anything is hit: `compare` accepts a candidate whenever its
 // t is below the initial 1e10, and the first acceptance already makes f0 >= 0
-__device__ __forceinline__ bool sphere_any(const Ray& r, V3 center) {
-    const V3 op = center - r.origin;
-    const float b = dot(op, r.direction);
-    float det = b * b - dot(op, op) + 1.0f * 1.0f;
-    if (det < 0.0f) return false;
-    det = sqrtf(det);
-    float t = b - det;
-    if (t < 0.0f) t = b + det;
-    if (t < 0.0f) return false;
-    return t < 1e10f;
-}
 __device__ __forceinline__ bool occluded(const Ray& r) {
-    bool any = false;
-    const float dotnd = dot(v3(0.0f, 1.0f, 0.0f), r.direction);
-    if (!(dotnd > 0.0f)) any = -(dot(r.origin, v3(0.0f, 1.0f, 0.0f)) + 0.0f) / dotnd < 1e10f;
-    any |= sphere_any(r, v3(-2.0f, 1.0f, 0.0f));
-    any |= sphere_any(r, v3(0.0f, 1.0f, 0.0f));
-    any |= sphere_any(r, v3(2.0f, 1.0f, 0.0f));
+    float t;
+    bool any = plane_t(1e10f, r, t);
+    any |= sphere_t(1e10f, r, v3(-2.0f, 1.0f, 0.0f), t);
+    any |= sphere_t(1e10f, r, v3(0.0f, 1.0f, 0.0f), t);
+    any |= sphere_t(1e10f, r, v3(2.0f, 1.0f, 0.0f), t);
     return any;
 }
 
@@ -195,34 +203,126 @@ __device__ __forceinline__ float fresnel(V3 h, V3 v, float f0) {
     return pow5(1.0f - clampf(dot(h, v), 0.0f, 1.0f)) * (1.0f - f0) + f0;
 }
 
-// rt.wgsl:128-158 `radiance` inside rt.wgsl:161-176 `fs_main`
-__device__ __forceinline__ V3 fs_main(float px, float py, const FrameConst& fc, uint32_t& rays) {
-    float ux = 2.0f * px / fc.res_x - 1.0f, uy = 2.0f * py / fc.res_y - 1.0f;
-    uy = -uy;
-    Ray ray = {v3(0.0f, 1.0f, 4.0f), normalize(v3(fc.aspect * ux, uy, -1.5f))};
-    V3 accum = splat(0.0f), attenuation = splat(1.0f);
-    const V3 sun_color = splat(1e3f);
-    for (int i = 0; i < SAMPLES; i++) {
-        const Hit hit = intersect_scene(ray);
+// a pixel's loop state (rt.wgsl:129-131 + the loop counter)
+struct Path { Ray ray; V3 accum, attenuation; int i; };
+
+// rt.wgsl:137-149, the light of a hit: `dir` = the direction the ray arrived with, `shadowed` = the shadow query of
+// rt.wgsl:122 hit something
+__device__ __forceinline__ void shade(Path& p, const Hit& hit, V3 dir, bool shadowed, const FrameConst& fc) {
+    const float f = fresnel(hit.normal, -dir, hit.f0);
+    V3 incoming = splat(0.0f);
+    if (!shadowed) incoming = incoming + clampf(dot(hit.normal, fc.sun_light), 0.0f, 1.0f) * splat(1e3f);
+    p.accum = p.accum + hit.color;
+    p.accum = p.accum + (1.0f - f) * p.attenuation * hit.color * incoming;
+    p.attenuation = p.attenuation * f;
+}
+
+// rt.wgsl:150-151, the mirror ray
+__device__ __forceinline__ Ray bounce(const Ray& ray, const Hit& hit) {
+    const V3 d = reflect(ray.direction, hit.normal);
+    return Ray{ray.origin + hit.t * ray.direction + EPSILON * d, d};
+}
+
+// rt.wgsl:122 with rt.wgsl:139
+__device__ __forceinline__ Ray shadow_ray(const Ray& ray, const Hit& hit, const FrameConst& fc) {
+    const V3 hit_pos = ray.origin + hit.t * ray.direction;
+    return Ray{hit_pos + EPSILON * fc.sun_light, fc.sun_light};
+}
+
+// one trip of rt.wgsl:134-156 on one lane; false when the path has ended
+__device__ __forceinline__ bool trip(Path& p, const FrameConst& fc, uint32_t& rays) {
+    const Hit hit = intersect_scene(p.ray);
+    ++rays;
+    if (hit.f0 >= 0.0f) {
         ++rays;
-        if (hit.f0 >= 0.0f) {
-            const float f = fresnel(hit.normal, -ray.direction, hit.f0);
-            const V3 hit_pos = ray.origin + hit.t * ray.direction;
-            V3 incoming = splat(0.0f);
-            ++rays;
-            if (!occluded(Ray{hit_pos + EPSILON * fc.sun_light, fc.sun_light}))
-                incoming = incoming + clampf(dot(hit.normal, fc.sun_light), 0.0f, 1.0f) * sun_color;
-            accum = accum + hit.color;
-            accum = accum + (1.0f - f) * attenuation * hit.color * incoming;
-            attenuation = attenuation * f;
-            const V3 d = reflect(ray.direction, hit.normal);
-            ray = Ray{ray.origin + hit.t * ray.direction + EPSILON * d, d};
-        } else {
-            accum = accum + get_sky_color(ray.direction, fc);
-            break;
+        shade(p, hit, p.ray.direction, occluded(shadow_ray(p.ray, hit, fc)), fc);
+        p.ray = bounce(p.ray, hit);
+        return ++p.i < SAMPLES;
+    }
+    p.accum = p.accum + get_sky_color(p.ray.direction, fc);
+    return false;
+}
+
+// The tail.  rt.wgsl's loop runs up to 1000 trips and the frame holds pixels that use them all: one dependent chain
+// per trip (query -> normal -> mirror ray) on a lane whose 31 neighbours have long finished.  Once a warp is down to
+// <= kGroupTail live paths, each path moves to a group of 4 lanes.  Lane k of the group tests primitive k (plane, s1,
+// s2, s3) of the primary query and the group takes the minimum (ties to the earlier primitive, as the sequential
+// `compare` of rt.wgsl:77-85 does); every lane of the group keeps the whole path state.  The loop is software-
+// pipelined: the next ray needs only the hit, not its light, so trip k's primary query and trip k-1's shadow query
+// (lane k tests primitive k again, a ballot ORs them) sit in one basic block and their chains interleave; the light of
+// trip k-1 is added before anything trip k adds, so every sum sees its terms in the shader's order.  Same operations
+// on the same values - bit-identical - on a much shorter critical path.
+__device__ __forceinline__ void finish_in_groups(unsigned live, bool& alive, Path& p, const FrameConst& fc, uint32_t& rays) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, g = lane >> 2, sub = lane & 3;
+    const bool has = g < __popc(live);
+    const int src = has ? (int)__fns(live, 0, g + 1) : lane;  // the g-th live lane
+    Path q;
+    q.ray.origin = v3(__shfl_sync(full, p.ray.origin.x, src), __shfl_sync(full, p.ray.origin.y, src), __shfl_sync(full, p.ray.origin.z, src));
+    q.ray.direction = v3(__shfl_sync(full, p.ray.direction.x, src), __shfl_sync(full, p.ray.direction.y, src), __shfl_sync(full, p.ray.direction.z, src));
+    q.accum = v3(__shfl_sync(full, p.accum.x, src), __shfl_sync(full, p.accum.y, src), __shfl_sync(full, p.accum.z, src));
+    q.attenuation = v3(__shfl_sync(full, p.attenuation.x, src), __shfl_sync(full, p.attenuation.y, src), __shfl_sync(full, p.attenuation.z, src));
+    q.i = __shfl_sync(full, p.i, src);
+    const float inf = __uint_as_float(0x7f800000u);
+    const V3 center = v3((float)(2 * sub - 4), 1.0f, 0.0f);  // of sphere `sub` (1..3); lane 0 of a group has the plane
+    bool galive = has, pending = false;  // pending: the previous trip's hit still waits for its light
+    Hit ph = surface(-1, 1e10f, q.ray);
+    V3 pdir = q.ray.direction;
+    Ray psr = Ray{q.ray.origin, fc.sun_light};
+    while (__any_sync(full, galive || pending)) {
+        float tp, ts, stp, sts;
+        const bool okp = plane_t(1e10f, q.ray, tp), oks = sphere_t(1e10f, q.ray, center, ts);
+        const bool sokp = plane_t(1e10f, psr, stp), soks = sphere_t(1e10f, psr, center, sts);
+        float t = (sub == 0 ? okp : oks) ? (sub == 0 ? tp : ts) : inf;
+        int which = sub;
+#pragma unroll
+        for (int m = 1; m <= 2; m <<= 1) {
+            const float ot = __shfl_xor_sync(full, t, m);
+            const int ow = __shfl_xor_sync(full, which, m);
+            if (ot < t || (ot == t && ow < which)) { t = ot; which = ow; }
+        }
+        const unsigned shadow_bits = __ballot_sync(full, pending && (sub == 0 ? sokp : soks));
+        if (pending) {
+            shade(q, ph, pdir, ((shadow_bits >> (g * 4)) & 15u) != 0u, fc);
+            pending = false;
+        }
+        if (galive) {
+            const bool is_hit = t < inf;
+            if (sub == 0) rays += is_hit ? 2u : 1u;
+            if (is_hit) {
+                ph = surface(which, t, q.ray);
+                pdir = q.ray.direction;
+                psr = shadow_ray(q.ray, ph, fc);
+                q.ray = bounce(q.ray, ph);
+                pending = true;
+                galive = ++q.i < SAMPLES;
+            } else {
+                q.accum = q.accum + get_sky_color(q.ray.direction, fc);
+                galive = false;
+            }
         }
     }
-    accum = accum / (float)SAMPLES;
+    // the r-th live lane's path ran on group r
+    const int back = alive ? 4 * __popc(live & ((1u << lane) - 1u)) : lane;
+    const V3 done = v3(__shfl_sync(full, q.accum.x, back), __shfl_sync(full, q.accum.y, back), __shfl_sync(full, q.accum.z, back));
+    if (alive) p.accum = done;
+    alive = false;
+}
+
+// rt.wgsl:128-158 `radiance` inside rt.wgsl:161-176 `fs_main`; called by all 32 lanes of a warp (inside = the lane has
+// a pixel)
+__device__ __forceinline__ V3 fs_main(float px, float py, bool inside, const FrameConst& fc, uint32_t& rays) {
+    float ux = 2.0f * px / fc.res_x - 1.0f, uy = 2.0f * py / fc.res_y - 1.0f;
+    uy = -uy;
+    Path p = {Ray{v3(0.0f, 1.0f, 4.0f), normalize(v3(fc.aspect * ux, uy, -1.5f))}, splat(0.0f), splat(1.0f), 0};
+    bool alive = inside;
+    for (;;) {
+        const unsigned live = __ballot_sync(0xffffffffu, alive);
+        if (live == 0u) break;
+        if (__popc(live) <= kGroupTail) { finish_in_groups(live, alive, p, fc, rays); break; }
+        if (alive) alive = trip(p, fc, rays);
+    }
+    const V3 accum = p.accum / (float)SAMPLES;
     return accum / 1.0f;
 }
 }  // namespace rt1
@@ -348,9 +448,12 @@ __global__ void __launch_bounds__(kThreads) frag_kernel(FrameConst fc, uint32_t 
     const uint32_t x = bx * kTileW + (warp & 1u) * 8u + (lane & 7u);
     const uint32_t y = by * kTileH + (warp >> 1) * 4u + (lane >> 3);
     uint32_t rays = 0;
-    if (x < width && y < height) {
-        const float px = (float)x + 0.5f, py = (float)y + 0.5f;
-        const V3 c = SHADER == 1 ? rt1::fs_main(px, py, fc, rays) : rt2::fs_main(px, py, fc, rays);
+    const bool inside = x < width && y < height;
+    const float px = (float)x + 0.5f, py = (float)y + 0.5f;
+    V3 c = splat(0.0f);
+    if (SHADER == 1) c = rt1::fs_main(px, py, inside, fc, rays);  // warp-collective
+    else if (inside) c = rt2::fs_main(px, py, fc, rays);
+    if (inside) {
         const size_t i = (size_t)y * width + x;
         if (linear) linear[i] = make_float4(c.x, c.y, c.z, 1.0f);
         if (rgba8) {
