@@ -325,6 +325,18 @@ def other_configs(device):
     out["D 100k spheres 1920x1080 64 spp (LBVH)"] = {"kernel_ms": round(st.kernel_ms, 3), "total_ms": round(st.total_ms, 3),
                                                     "rays": int(st.rays), "mrays_s": round(st.rays / st.kernel_ms / 1e3, 1),
                                                     "bvh_nodes": int(st.bvh_nodes)}
+    # config D's roofline is L2 traffic - counted node visits x 32 B + leaf tests x 16 B from an
+    # instrumented (untimed) run of the same traversal, over the timed kernel, against the streaming-from-L2 read
+    # bandwidth measured on this box by the same call
+    ws = m.walk_stats(64, max_depth=DEPTH)
+    l2_bytes = ws.node_visits * ws.node_bytes + ws.leaf_tests * ws.leaf_bytes
+    gbs = l2_bytes / (st.kernel_ms * 1e-3) / 1e9
+    out["D 100k spheres 1920x1080 64 spp (LBVH)"]["l2_roofline"] = {
+        "node_visits": int(ws.node_visits), "leaf_tests": int(ws.leaf_tests), "rays_instrumented": int(ws.rays),
+        "visits_per_ray": round(ws.node_visits / max(1, ws.rays), 2), "leaf_tests_per_ray": round(ws.leaf_tests / max(1, ws.rays), 2),
+        "bytes": int(l2_bytes), "achieved_gbs": round(gbs, 1), "peak_gbs": round(float(ws.l2_read_gbs), 1),
+        "frac": round(gbs / ws.l2_read_gbs, 4) if ws.l2_read_gbs > 0 else None,
+        "peak_source": "forma_rt_walk_stats_get: 32 MiB buffer streamed out of L2, 8 passes, CUDA events (measured here)"}
     m.close()
     return out
 

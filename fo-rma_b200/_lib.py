@@ -46,6 +46,12 @@ class Stats(ctypes.Structure):
                 ("sm_clock_khz", ctypes.c_uint32)]
 
 
+class WalkStats(ctypes.Structure):
+    _fields_ = [("rays", ctypes.c_uint64), ("node_visits", ctypes.c_uint64), ("leaf_tests", ctypes.c_uint64),
+                ("node_bytes", ctypes.c_uint32), ("leaf_bytes", ctypes.c_uint32), ("bvh_nodes", ctypes.c_uint32),
+                ("l2_read_gbs", ctypes.c_float)]
+
+
 assert ctypes.sizeof(Object) == 64 and ctypes.sizeof(Camera) == 104
 
 _vp, _u8p, _fp = ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint8), ctypes.POINTER(ctypes.c_float)
@@ -90,6 +96,7 @@ SYMBOLS = {
     "forma_rt_synchronize": (_int, [_vp]),
     "forma_rt_stats_get": (_int, [_vp, ctypes.POINTER(Stats)]),
     "forma_rt_write_png": (_int, [ctypes.c_char_p, _vp, _u32, _u32]),
+    "forma_rt_walk_stats_get": (_int, [_vp, _u32, _u32, ctypes.POINTER(WalkStats)]),
 }
 
 

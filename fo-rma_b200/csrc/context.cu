@@ -102,6 +102,8 @@ struct forma_rt {
     uint8_t srgb_lut[256];            // color_utils::srgb_encode as a table (color_utils.rs:49-66)
     DevBuf<float4> d_rad, d_acc;      // tree mode: per-path radiance of a chunk of samples, in-order running sum
     DevBuf<unsigned int> d_job;       // tree mode: job queue head
+    DevBuf<unsigned long long> d_walk; // forma_rt_walk_stats_get: node-visit and leaf-test counters
+    bool count_walk = false;          // the next render_on_device uses the instrumented tree kernel
     unsigned long long* d_rays = nullptr;
     unsigned long long* h_rays = nullptr;  // pinned
 
@@ -117,7 +119,7 @@ struct forma_rt {
         d_spheres.release(); d_tris.release(); d_planes.release(); d_material.release();
         d_sphere_obj.release(); d_tri_obj.release(); d_plane_obj.release(); d_kindmat.release(); d_ids.release();
         d_segments.release(); d_rgb.release(); d_sum.release(); d_prim.release(); d_t.release();
-        d_rad.release(); d_acc.release(); d_job.release(); d_prog.release();
+        d_rad.release(); d_acc.release(); d_job.release(); d_prog.release(); d_walk.release();
         bvh.release();
         if (d_rays) cudaFree(d_rays);
         if (h_rays) cudaFreeHost(h_rays);
@@ -599,6 +601,7 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
         P.rad = c->d_rad.p; P.acc = c->d_acc.p; P.job_counter = c->d_job.p;
         P.rad_chunk = (uint32_t)chunk;
         P.refill = c->refill; P.leaf_batch = c->leaf_batch;
+        P.walk_counters = c->count_walk ? c->d_walk.p : nullptr;
     }
     if (c->fast_div < 0) {  // once per handle: width and height never change
         c->fast_div = 0;
@@ -889,6 +892,54 @@ int forma_rt_stats_get(forma_rt* ctx, forma_rt_stats* out) {
         ctx->stats_pending = false;
     }
     *out = ctx->stats;
+    return FORMA_RT_OK;
+}
+
+int forma_rt_walk_stats_get(forma_rt* ctx, uint32_t spp, uint32_t max_depth, forma_rt_walk_stats* out) {
+    NEED_DEV(ctx);
+    if (!out) return fail(FORMA_RT_EINVAL, "forma_rt_walk_stats_get: out is null");
+    forma_rt_walk_stats ws{};
+    ws.node_bytes = 32;
+    int rc = ensure_scene(ctx);
+    if (rc) return rc;
+    cudaStream_t s = ctx->stream;
+    const size_t npix = (size_t)ctx->width * ctx->height;
+    CU_TRY(ctx->d_walk.ensure(2));
+    CU_TRY(cudaMemsetAsync(ctx->d_walk.p, 0, 2 * sizeof(unsigned long long), s));
+    CU_TRY(ctx->d_sum.ensure(npix));
+    ctx->count_walk = true;
+    rc = render_on_device(ctx, spp, 0, max_depth, ctx->flags, nullptr, ctx->d_sum.p, s);
+    ctx->count_walk = false;
+    if (rc) return rc;
+    unsigned long long counts[2] = {0, 0}, rays = 0;
+    CU_TRY(cudaMemcpyAsync(counts, ctx->d_walk.p, sizeof counts, cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaMemcpyAsync(&rays, ctx->d_rays, sizeof rays, cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    ctx->stats_pending = false;  // an instrumented frame is not a timed one
+    ws.rays = rays; ws.node_visits = counts[0]; ws.leaf_tests = counts[1];
+    ws.bvh_nodes = ctx->view.bvh_nodes ? ctx->stats.bvh_nodes : 0;
+    ws.leaf_bytes = ctx->stats.n_triangles && !ctx->stats.n_spheres ? 48 : 16;
+    {   // streaming read out of L2: 32 MiB (a quarter of the 126 MB L2), one warm-up pass, then 8 timed passes
+        const size_t bytes = 32u << 20;
+        const uint32_t passes = 8;
+        void* buf = nullptr;
+        uint32_t* sink = nullptr;
+        CU_TRY(cudaMalloc(&buf, bytes + 256));
+        sink = (uint32_t*)((char*)buf + bytes);
+        cudaError_t e = cudaMemsetAsync(buf, 0x5a, bytes + 256, s);
+        size_t per_pass = 0;
+        if (e == cudaSuccess) e = forma::launch_l2_read(buf, bytes, 1, sink, ctx->sm_count, s, &per_pass);
+        if (e == cudaSuccess) e = cudaEventRecord(ctx->ev_begin, s);
+        if (e == cudaSuccess) e = forma::launch_l2_read(buf, bytes, passes, sink, ctx->sm_count, s, nullptr);
+        if (e == cudaSuccess) e = cudaEventRecord(ctx->ev_end, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        float ms = 0.0f;
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end);
+        cudaFree(buf);
+        if (e != cudaSuccess) return fail(FORMA_RT_ECUDA, std::string("l2 read microbenchmark: ") + cudaGetErrorString(e));
+        ws.l2_read_gbs = ms > 0.0f ? (float)((double)per_pass * passes / (ms * 1e-3) / 1e9) : 0.0f;
+    }
+    *out = ws;
     return FORMA_RT_OK;
 }
 

@@ -98,6 +98,8 @@ struct RenderParams {
     uint32_t chunk_base, chunk_k; // samples [chunk_base, chunk_base + chunk_k) are traced by this launch
     uint32_t leaf_batch;       // lanes that must stop before the warp looks at its waiting leaves
     uint32_t refill;           // refill a warp's finished lanes once this many are idle
+    unsigned long long* walk_counters;  // nullable: [0] += internal nodes visited, [1] += leaf primitives tested (the
+                                        // instrumented instantiation of render_tree_kernel; forma_rt_walk_stats)
 };
 
 struct PrimaryParams {

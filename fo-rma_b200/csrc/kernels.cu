@@ -202,6 +202,9 @@ constexpr int kBatchSamples = 8;
 #ifndef FORMA_TREE_MIN_BLOCKS
 #define FORMA_TREE_MIN_BLOCKS 8  // 64 registers: 32 resident warps / SM (profiles/r01p_occ.txt: A 134 -> 122 ms, D 142 -> 138 ms)
 #endif
+// COUNT = true is the instrumented instantiation (forma_rt_walk_stats): the same traversal, plus two per-lane
+// counters - internal nodes visited and leaf primitives tested - summed into P.walk_counters.  Never timed.
+template <bool COUNT>
 __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_kernel(const __grid_constant__ RenderParams P) {
     const SceneView& S = P.scene;
     const float4 *sph = S.spheres, *tri = S.tris;
@@ -218,6 +221,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
     const bool no_jitter = P.flags & FORMA_RT_NO_JITTER, pinhole = P.flags & FORMA_RT_PINHOLE;
 
     uint32_t rays = 0;
+    unsigned long long n_nodes = 0, n_leaves = 0;  // COUNT only
     int astack[kMaxDepthCap];   // list indices of the hit objects: attenuations multiply innermost first
     __shared__ int2 stack_smem[kSmemStack * kWalkBlock];
     int2 stack_local[kStackCap - kSmemStack];
@@ -342,6 +346,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
                         if (__int_as_float(e.y) <= h.closest) W.node = e.x;  // else: stays kWalkPop
                     }
                 }
+                if (COUNT && walking && W.node >= 0) ++n_nodes;
                 if (walking && W.node >= 0) walk_inner(S, W, wstack, h.closest);
                 const bool busy = walking && (W.node >= 0 || W.node == kWalkPop);
                 const int stopped = 32 - __popc(__ballot_sync(kFull, busy));
@@ -352,6 +357,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
                 const int idle = __popc(__ballot_sync(kFull, !lane_done && phase != kWalk));
                 if (idle >= (int)P.refill || (stopped == 32 && leaves == 0u)) break;
                 if (at_leaf) {
+                    if (COUNT) ++n_leaves;
                     const int p = ~W.node;
                     if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w);
                     else try_triangle(S, tri, p - S.n_spheres, o, d, h, w);
@@ -365,6 +371,13 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
     // closest-hit query count: one atomic per warp
     uint32_t wr = __reduce_add_sync(kFull, rays);
     if (lane == 0 && wr) atomicAdd(P.rays, (unsigned long long)wr);
+    if (COUNT) {
+        for (int m = 16; m >= 1; m >>= 1) {
+            n_nodes += __shfl_xor_sync(kFull, n_nodes, m);
+            n_leaves += __shfl_xor_sync(kFull, n_leaves, m);
+        }
+        if (lane == 0) { atomicAdd(P.walk_counters, n_nodes); atomicAdd(P.walk_counters + 1, n_leaves); }
+    }
 }
 
 // tracer.rs:170-184 for tree mode: acc[p] += rad[0][p], rad[1][p], ... in sample order; after the last
@@ -517,7 +530,9 @@ static cudaError_t launch_render_tree(RenderParams P, int sm_count, cudaStream_t
     if (!P.rad || !P.acc || !P.job_counter || P.rad_chunk == 0) return cudaErrorInvalidValue;
     const uint64_t tiles = (uint64_t)((P.width + 7) / 8) * ((P.height + 3) / 4);
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_tree_kernel, kBlock, 0);
+    const bool count = P.walk_counters != nullptr;
+    cudaError_t e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_tree_kernel<true>, kBlock, 0)
+                          : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_tree_kernel<false>, kBlock, 0);
     if (e != cudaSuccess) return e;
     const int grid = sm_count * (per_sm > 0 ? per_sm : 1);
     const size_t npix = (size_t)P.width * P.height;
@@ -526,7 +541,8 @@ static cudaError_t launch_render_tree(RenderParams P, int sm_count, cudaStream_t
         while (tiles * k >= (1ull << 32)) k = (k + 1) / 2;  // batch indices are 32-bit
         P.chunk_base = base; P.chunk_k = k;
         if ((e = cudaMemsetAsync(P.job_counter, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
-        render_tree_kernel<<<grid, kBlock, 0, stream>>>(P);
+        if (count) render_tree_kernel<true><<<grid, kBlock, 0, stream>>>(P);
+        else render_tree_kernel<false><<<grid, kBlock, 0, stream>>>(P);
         accumulate_kernel<<<stream_grid(npix, sm_count), 256, 0, stream>>>(P, base == 0, base + k >= P.spp);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         *launches += 2;
@@ -563,6 +579,40 @@ cudaError_t launch_primary_hits(const PrimaryParams& P, cudaStream_t stream) {
     } else {
         primary_hits_kernel<kScanGlobal><<<grid, kBlock, 0, stream>>>(P);
     }
+    return cudaGetLastError();
+}
+
+// Streaming-from-L2 read microbenchmark (the denominator of config D's L2 roofline is measured on the
+// box, not assumed): per pass the grid reads the buffer once, 16 bytes per lane and load (ld.global.cg: L2, not L1),
+// 8 loads in flight per lane; the XOR of everything keeps the loads alive.  The caller runs an untimed pass first, so
+// the timed passes hit L2.
+__global__ void __launch_bounds__(256) l2_read_kernel(const uint4* __restrict__ buf, size_t n16, uint32_t passes,
+                                                      uint32_t* __restrict__ sink) {
+    uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (uint32_t p = 0; p < passes; ++p) {
+        // a different starting phase per CTA and pass, so that CTAs do not march through the buffer in lock step
+        size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x + (size_t)p * 977u * blockDim.x) % n16;
+        const size_t per_thread = n16 / stride;
+        for (size_t k = 0; k + 8 <= per_thread; k += 8) {
+            uint4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { v[u] = __ldcg(buf + i); i += stride; if (i >= n16) i -= n16; }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { acc.x ^= v[u].x; acc.y ^= v[u].y; acc.z ^= v[u].z; acc.w ^= v[u].w; }
+        }
+    }
+    if ((acc.x ^ acc.y ^ acc.z ^ acc.w) == 0x9e3779b9u) *sink = acc.x;  // practically never: keeps the loads live
+}
+
+cudaError_t launch_l2_read(const void* buf, size_t bytes, uint32_t passes, uint32_t* sink, int sm_count, cudaStream_t stream,
+                           size_t* bytes_per_pass) {
+    const size_t n16 = bytes / 16;
+    const int grid = sm_count * 2;  // 16 warps / SM, 8 x 16 B in flight per lane
+    const size_t stride = (size_t)grid * 256, rounds = n16 / stride / 8;
+    if (rounds == 0) return cudaErrorInvalidValue;
+    if (bytes_per_pass) *bytes_per_pass = rounds * 8 * stride * 16;
+    l2_read_kernel<<<grid, 256, 0, stream>>>((const uint4*)buf, n16, passes, sink);
     return cudaGetLastError();
 }
 

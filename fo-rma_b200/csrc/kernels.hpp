@@ -18,4 +18,9 @@ cudaError_t launch_tonemap(const float4* sum, uint32_t spp, uint64_t begin, uint
 cudaError_t launch_reduce_tonemap(const float4* const* peers, int n_peers, uint32_t spp, uint64_t begin, uint64_t end,
                                   uint8_t* rgb, float4* sum_out, int sm_count, cudaStream_t stream);
 
+// the grid reads buf `passes` times through L2; *bytes_per_pass = what one pass reads (bytes rounded down to whole
+// rounds of 8 loads per thread)
+cudaError_t launch_l2_read(const void* buf, size_t bytes, uint32_t passes, uint32_t* sink, int sm_count, cudaStream_t stream,
+                           size_t* bytes_per_pass);
+
 }  // namespace forma

@@ -204,6 +204,13 @@ class TraceModel:
         check(_lib.lib().forma_rt_stats_get(self._h, ctypes.byref(s)))
         return s
 
+    def walk_stats(self, spp: int, *, max_depth: int = MAX_DEPTH) -> _lib.WalkStats:
+        """Instrumented (untimed) frame: node visits / leaf tests of the LBVH walk, plus this device's measured
+        streaming-from-L2 read bandwidth (config D's L2 roofline)."""
+        ws = _lib.WalkStats()
+        check(_lib.lib().forma_rt_walk_stats_get(self._h, spp, max_depth, ctypes.byref(ws)))
+        return ws
+
     # device-resident variants: pointers are raw CUDA addresses (e.g. torch.Tensor.data_ptr())
     def render_device(self, spp, sample_offset, max_depth, d_rgb: int | None, d_sum: int | None, stream: int = 0):
         check(_lib.lib().forma_rt_render_device(self._h, spp, sample_offset, max_depth, d_rgb, d_sum, stream or None))

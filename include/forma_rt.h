@@ -104,6 +104,17 @@ typedef struct forma_rt_stats {
     uint32_t sm_clock_khz;  /* cudaDevAttrClockRate */
 } forma_rt_stats;
 
+/* forma_rt_walk_stats: what one frame's LBVH traversal touches (SURVEY 8(d), config D's L2 roofline) */
+typedef struct forma_rt_walk_stats {
+    uint64_t rays;          /* closest-hit queries of the instrumented frame */
+    uint64_t node_visits;   /* internal nodes whose two child boxes were tested */
+    uint64_t leaf_tests;    /* leaf primitives handed to the sphere / triangle test */
+    uint32_t node_bytes;    /* bytes fetched per node visit (one 32-byte record) */
+    uint32_t leaf_bytes;    /* bytes fetched per leaf test (a sphere: 16; a triangle: 48) */
+    uint32_t bvh_nodes;     /* 0: the scene is scanned, there is no walk */
+    float l2_read_gbs;      /* streaming-from-L2 read bandwidth measured on this device by the same call */
+} forma_rt_walk_stats;
+
 /* ---- life cycle ------------------------------------------------------------------------------ */
 /* tracer::create_model (tracer.rs:19-28): width x height model with Scene::new's content
  * (scene.rs:10-15: Camera::new + scenes::get_simple_scene). */
@@ -203,6 +214,12 @@ FORMA_RT_API int forma_rt_device_free(forma_rt* ctx, void* d_ptr);
 FORMA_RT_API int forma_rt_synchronize(forma_rt* ctx);
 
 /* ---- misc -------------------------------------------------------------------------------------- */
+/* Instrumented (untimed) frame: the same traversal as forma_rt_render(spp, 0, max_depth) with per-lane counters,
+ * through a second instantiation of the tree kernel; no frame is returned.  Also runs a streaming read of a 32 MiB
+ * buffer out of L2 (one warm-up pass, then timed passes, CUDA events) and reports its bandwidth.  Added; the
+ * reference has no acceleration structure. */
+FORMA_RT_API int forma_rt_walk_stats_get(forma_rt* ctx, uint32_t spp, uint32_t max_depth, forma_rt_walk_stats* out);
+
 FORMA_RT_API int forma_rt_stats_get(forma_rt* ctx, forma_rt_stats* out);
 /* color_utils::srgb_encode (color_utils.rs:49-66) in place on nbytes of device RGB8 (4-byte aligned);
  * the function maps u8 -> u8, forma_rt_srgb_table returns that map (host, no device needed). */

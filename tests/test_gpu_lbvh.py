@@ -107,3 +107,37 @@ def test_lbvh_rejects_interleaved_planes():
     ids, _ = m2.primary_hits()
     assert m2.stats().accel_in_use == _lib.ACCEL_BRUTE
     assert np.array_equal(ids, ob.primary_hits(objs, ob.camera_new(32, 32), 32, 32)[0])
+
+
+def test_walk_stats_instrumented_frame():
+    """forma_rt_walk_stats_get: the instrumented instantiation walks the same tree for the same rays."""
+    rng = np.random.default_rng(3)
+    n = 5000
+    recs = np.zeros(n, dtype=forma_b200.tracer.OBJECT_DTYPE)
+    recs["kind"] = _lib.SPHERE
+    recs["material"] = rng.integers(0, 3, n)
+    recs["id"] = np.arange(n)
+    recs["fuzz"] = rng.uniform(0, 0.5, n)
+    recs["color"] = rng.uniform(0.1, 0.9, (n, 3))
+    recs["a"] = np.stack([rng.uniform(-6, 6, n), rng.uniform(-3, 3, n), rng.uniform(-9, -2, n)], 1)
+    recs["b"][:, 0] = rng.uniform(0.05, 0.2, n)
+    w, h, spp = 160, 90, 3
+    m = forma_b200.create_model(w, h, seed=2, accel=_lib.ACCEL_LBVH)
+    m.scene.load_objects(recs)
+    rgb, lin = m.render(spp, want_linear=True)
+    rays = m.stats().rays
+    ws = m.walk_stats(spp)
+    assert ws.rays == rays and ws.bvh_nodes == n - 1 and ws.node_bytes == 32 and ws.leaf_bytes == 16
+    assert ws.node_visits > ws.leaf_tests > 0
+    # every ray that is not culled by the scene's bounding sphere visits at least the root
+    assert ws.node_visits <= rays * 2 * 64 and ws.node_visits >= 0.2 * rays
+    assert 500.0 < ws.l2_read_gbs < 40000.0
+    # the instrumented frame leaves the product path untouched: the next render is the same frame again
+    rgb2, lin2 = m.render(spp, want_linear=True)
+    assert np.array_equal(rgb, rgb2) and np.array_equal(lin.view(np.uint32), lin2.view(np.uint32))
+    assert m.stats().rays == rays
+    # a scanned scene has no walk
+    b = forma_b200.create_model(64, 48, seed=1, accel=_lib.ACCEL_BRUTE)
+    b.scene.load_builtin(2)
+    ws = b.walk_stats(2)
+    assert ws.bvh_nodes == 0 and ws.node_visits == 0 and ws.leaf_tests == 0 and ws.rays > 0
