@@ -6,6 +6,7 @@
 //
 //   frontend_headless <width> <height> <frames> [--keys 0x0a] [--dt 0.016] [--scene file.json] [--png out/basic.png]
 //                     [--spp 50] [--seed 0]
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -66,8 +67,11 @@ int main(int argc, char** argv) {
                 model.scene.objects[0].translate(translation);  // macroquad.rs:66
                 model.scene.objects[0].rotate(orientation);     // macroquad.rs:67
             }
+            const auto t0 = std::chrono::steady_clock::now();
             tracer::update(model, keys, dt);                    // macroquad.rs:68
-            std::printf("frame %d: %zu bytes, fnv1a %016llx\n", frame, model.pixels.size(), (unsigned long long)fnv1a(model.pixels));
+            const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+            std::printf("frame %d: %zu bytes, fnv1a %016llx, %.3f ms\n", frame, model.pixels.size(),
+                        (unsigned long long)fnv1a(model.pixels), ms);
         }
         if (!png.empty()) {
             tracer::save_image(model, spp, png.c_str());        // macroquad.rs:59-61
