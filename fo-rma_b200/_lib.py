@@ -11,7 +11,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libforma_rt.so")
+# FORMA_RT_LIB: another build of the same library (occupancy / flag experiments); never a different implementation
+LIB_PATH = os.environ.get("FORMA_RT_LIB") or os.path.join(_HERE, "libforma_rt.so")
 
 OK, EINVAL, EJSON, ECUDA, EIO, ENOMEM = 0, -1, -2, -3, -4, -5
 NO_JITTER, PINHOLE, HOST_ONLY, SRGB_OUT = 1, 2, 4, 8

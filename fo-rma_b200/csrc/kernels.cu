@@ -62,7 +62,7 @@ __device__ __forceinline__ void write_out(const RenderParams& P, float3 col, uin
 }
 
 #ifndef FORMA_SCAN_MIN_BLOCKS
-#define FORMA_SCAN_MIN_BLOCKS 6
+#define FORMA_SCAN_MIN_BLOCKS 7  // 72 registers, no spills, 28 resident warps / SM (profiles/r04i_occ.txt: C 119.8 -> 121.5 Grays/s)
 #endif
 template <int MODE>
 __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(const __grid_constant__ RenderParams P) {
