@@ -59,7 +59,8 @@ struct DevBuf {
 
 constexpr int kSmemStageLimit = 96 * 1024;   // stage spheres+tris in shared memory up to this size
 constexpr uint32_t kBvhThreshold = 16;       // ACCEL_AUTO: LBVH at or above this many spheres + triangles
-constexpr size_t kRadBudget = 1ull << 30;    // tree mode: bytes of per-path radiance kept between trace and accumulate
+constexpr size_t kRadBudget = 4ull << 30;    // tree mode: bytes of per-path radiance kept between trace and accumulate
+                                             // (64 samples of a 1080p frame = 2.1 GB in ONE launch: every launch ends with a drain)
 
 }  // namespace
 

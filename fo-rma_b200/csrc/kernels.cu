@@ -197,7 +197,13 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
 //    The warp walks until `refill` lanes have finished their walk (or none is walking), then those
 //    lanes shade, scatter or draw their next job and rejoin.
 enum : int { kNewPath = 0, kStart = 1, kWalk = 2, kShade = 3 };
-constexpr int kBatchSamples = 8;
+// A batch is what a warp holds when the queue runs dry, i.e. the drain at the end of a launch: at 8 samples (256
+// paths, ~4 ms of a warp's time on config D) the tail cost 4-5 ms per launch - nothing on a 230 ms launch, 15 % of the
+// 30 ms launch each GPU of an 8-way tile split runs (tools/partition_probe.py: 36.3 -> 32.2 ms at 2 samples).
+#ifndef FORMA_BATCH_SAMPLES
+#define FORMA_BATCH_SAMPLES 2
+#endif
+constexpr int kBatchSamples = FORMA_BATCH_SAMPLES;
 
 #ifndef FORMA_TREE_MIN_BLOCKS
 #define FORMA_TREE_MIN_BLOCKS 8  // 64 registers: 32 resident warps / SM (profiles/r01p_occ.txt: A 134 -> 122 ms, D 142 -> 138 ms)

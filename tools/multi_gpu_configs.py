@@ -58,9 +58,15 @@ m = forma_b200.create_model(1920, 1080, device=local, seed=0)
 m.scene.load_json(json.dumps(gen.generate(100_000))); m.scene.camera.use_json()
 tx = TileExchange(m, dist, dev)
 ms = timed(lambda: tx.frame(args.spp_d, 50, ts.cuda_stream), args.reps)
+st = m.stats()
+per_rank = torch.zeros(world, 2, dtype=torch.float64, device=dev)
+per_rank[rank, 0], per_rank[rank, 1] = float(st.kernel_ms), float(st.rays)
+dist.all_reduce(per_rank)
 rays = total_rays(m)
 if rank == 0:
     print(json.dumps({"case": f"D 100k spheres 1920x1080 {args.spp_d} spp tile-interleaved", "n_gpus": world, "ms_per_frame": round(ms, 3),
-                      "rays": int(rays), "mrays_s": round(rays / ms / 1e3, 1), "exchange": tx.mode}), flush=True)
+                      "rays": int(rays), "mrays_s": round(rays / ms / 1e3, 1), "exchange": tx.mode,
+                      "kernel_ms_per_rank": [round(x, 2) for x in per_rank[:, 0].tolist()],
+                      "mrays_per_rank": [round(x / 1e6, 1) for x in per_rank[:, 1].tolist()]}), flush=True)
 dist.barrier()
 dist.destroy_process_group()
