@@ -89,6 +89,8 @@ SYMBOLS = {
     "forma_rt_render_device": (_int, [_vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "forma_rt_tonemap_device": (_int, [_vp, _vp, _u32, _u64, _u64, _vp, _vp]),
     "forma_rt_reduce_tonemap_device": (_int, [_vp, ctypes.POINTER(_vp), _u32, _u32, _u64, _u64, _vp, _vp, _vp]),
+    "forma_rt_flag_set_device": (_int, [_vp, _vp, _u32, _vp]),
+    "forma_rt_flag_wait_device": (_int, [_vp, ctypes.POINTER(_vp), _u32, _u32, _vp]),
     "forma_rt_ipc_export": (_int, [_vp, _vp, _vp]),
     "forma_rt_ipc_open": (_int, [_vp, _vp, ctypes.POINTER(_vp)]),
     "forma_rt_ipc_close": (_int, [_vp, _vp]),

@@ -832,6 +832,22 @@ int forma_rt_reduce_tonemap_device(forma_rt* ctx, const void* const* d_peer_sums
     return FORMA_RT_OK;
 }
 
+int forma_rt_flag_set_device(forma_rt* ctx, void* d_flag, uint32_t value, void* stream) {
+    NEED_DEV(ctx);
+    if (!d_flag || ((uintptr_t)d_flag & 3u)) return fail(FORMA_RT_EINVAL, "forma_rt_flag_set_device: bad flag pointer");
+    CU_TRY(forma::launch_flag_set((uint32_t*)d_flag, value, stream ? (cudaStream_t)stream : ctx->stream));
+    return FORMA_RT_OK;
+}
+
+int forma_rt_flag_wait_device(forma_rt* ctx, const void* const* d_flags, uint32_t n, uint32_t value, void* stream) {
+    NEED_DEV(ctx);
+    if (!d_flags || n == 0 || n > 16) return fail(FORMA_RT_EINVAL, "forma_rt_flag_wait_device: 1..16 flags");
+    for (uint32_t i = 0; i < n; ++i)
+        if (!d_flags[i] || ((uintptr_t)d_flags[i] & 3u)) return fail(FORMA_RT_EINVAL, "forma_rt_flag_wait_device: bad flag pointer");
+    CU_TRY(forma::launch_flag_wait((const uint32_t* const*)d_flags, (int)n, value, stream ? (cudaStream_t)stream : ctx->stream));
+    return FORMA_RT_OK;
+}
+
 int forma_rt_ipc_export(forma_rt* ctx, void* d_ptr, uint8_t handle[64]) {
     NEED_DEV(ctx);
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
@@ -860,6 +876,7 @@ int forma_rt_device_alloc(forma_rt* ctx, size_t bytes, void** d_ptr) {
     if (!d_ptr) return fail(FORMA_RT_EINVAL, "forma_rt_device_alloc: d_ptr is null");
     CU_TRY(cudaMalloc(d_ptr, bytes ? bytes : 1));
     ctx->scratch.push_back(*d_ptr);
+    CU_TRY(cudaMemset(*d_ptr, 0, bytes ? bytes : 1));  // flags start at 0; frames start black
     return FORMA_RT_OK;
 }
 

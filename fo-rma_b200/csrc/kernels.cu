@@ -646,4 +646,40 @@ cudaError_t launch_reduce_tonemap(const float4* const* peers, int n_peers, uint3
     return cudaGetLastError();
 }
 
+// ---- stream-ordered flags in peer-visible memory ------------------------------------------------------------
+// The sample-split exchange orders its kernels ACROSS GPUs with these instead of host-side barriers: a rank raises
+// its flag once its partial sums are complete, and the peers' reduce kernels are queued behind a wait on it.
+// Release / acquire at system scope; the flag lives in memory the peers map through CUDA IPC (NVLink).
+__global__ void flag_set_kernel(uint32_t* flag, uint32_t value) {
+    __threadfence_system();  // everything earlier in this stream is visible system-wide before the flag moves
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+
+struct FlagPtrs { const uint32_t* f[kMaxPeers]; };
+
+// one thread per flag spins until its flag has reached `value` (wrap-safe signed distance)
+__global__ void flag_wait_kernel(const __grid_constant__ FlagPtrs p, int n, uint32_t value) {
+    if ((int)threadIdx.x < n) {
+        uint32_t x;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(x) : "l"(p.f[threadIdx.x]) : "memory");
+        } while ((int32_t)(x - value) < 0);
+    }
+    __syncthreads();
+    __threadfence_system();
+}
+
+cudaError_t launch_flag_set(uint32_t* flag, uint32_t value, cudaStream_t stream) {
+    flag_set_kernel<<<1, 1, 0, stream>>>(flag, value);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_flag_wait(const uint32_t* const* flags, int n, uint32_t value, cudaStream_t stream) {
+    if (n < 1 || n > kMaxPeers) return cudaErrorInvalidValue;
+    FlagPtrs pp{};
+    for (int i = 0; i < n; ++i) pp.f[i] = flags[i];
+    flag_wait_kernel<<<1, kMaxPeers, 0, stream>>>(pp, n, value);
+    return cudaGetLastError();
+}
+
 }  // namespace forma

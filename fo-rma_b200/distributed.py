@@ -61,11 +61,20 @@ def gather_bytes(dist, payload: bytes, device) -> list[bytes]:
 
 
 class FusedExchange:
-    """Sample-split exchange over peer memory: every rank exports its float4 sum buffer (and rank 0
-    its RGB8 frame) through CUDA IPC; after a barrier each rank runs reduce_tonemap_kernel on its
-    pixel stripe — peer loads over NVLink, rank-order sum, tone-map, RGB8 stored into rank 0's frame."""
+    """Sample-split exchange over peer memory, with no host-side barrier in the frame.
 
-    mode = "fused peer-memory reduce+tonemap (CUDA IPC over NVLink)"
+    Every rank exports two float4 sum buffers (double-buffered) and two flags through CUDA IPC, rank 0 its RGB8 frame
+    as well.  Frame e (1, 2, ...) on every rank, all stream-ordered:
+        wait   peers' done  >= e - 2      their reduce of frame e - 2 has finished reading my sum[e & 1]
+        render my samples -> sum[e & 1]
+        set    my ready = e
+        wait   peers' ready >= e          their partial sums of frame e are complete in their HBM
+        reduce_tonemap on my pixel stripe: peer loads over NVLink, rank-order sum, tone-map, RGB8 into rank 0's frame
+        set    my done = e
+        rank 0: wait peers' done >= e     the frame is complete in rank 0's memory
+    A rank never waits for more than the data it needs; nothing returns to the host until the caller synchronises."""
+
+    mode = "fused peer-memory reduce+tonemap, flag-ordered (CUDA IPC over NVLink, no barrier per frame)"
 
     def __init__(self, model, dist, device):
         import ctypes
@@ -73,31 +82,60 @@ class FusedExchange:
         self.m, self.dist = model, dist
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
         self.npix = model.width * model.height
-        p, q = ctypes.c_void_p(), ctypes.c_void_p()
-        _lib.check(_lib.lib().forma_rt_device_alloc(model._h, self.npix * 16, ctypes.byref(p)))
-        _lib.check(_lib.lib().forma_rt_device_alloc(model._h, self.npix * 3, ctypes.byref(q)))
-        self.sum, self.rgb = p.value, q.value
-        handles = gather_bytes(dist, model.ipc_export(self.sum) + model.ipc_export(self.rgb), device)
-        self.peer_sums = [self.sum if r == self.rank else model.ipc_open(h[:64]) for r, h in enumerate(handles)]
-        self.rgb0 = self.rgb if self.rank == 0 else model.ipc_open(handles[0][64:])
+
+        def alloc(nbytes):
+            p = ctypes.c_void_p()
+            _lib.check(_lib.lib().forma_rt_device_alloc(model._h, nbytes, ctypes.byref(p)))  # zero-filled
+            return p.value
+
+        self.sums = [alloc(self.npix * 16), alloc(self.npix * 16)]
+        self.rgb = alloc(self.npix * 3)
+        self.flags = alloc(256)  # ready at +0, done at +128 (separate lines)
+        payload = b"".join(model.ipc_export(p) for p in (self.sums[0], self.sums[1], self.rgb, self.flags))
+        handles = gather_bytes(dist, payload, device)  # a collective: every rank's flags are zero before anyone waits
+
+        def peer(r, k, own):
+            return own if r == self.rank else model.ipc_open(handles[r][64 * k:64 * (k + 1)])
+
+        self.peer_sums = [[peer(r, b, self.sums[b]) for r in range(self.world)] for b in (0, 1)]
+        self.rgb0 = peer(0, 2, self.rgb)
+        peer_flags = [peer(r, 3, self.flags) for r in range(self.world)]
+        self.ready = [f for f in peer_flags]
+        self.done = [f + 128 for f in peer_flags]
         self.stripe = pixel_stripe(self.rank, self.world, self.npix)
+        self.epoch = 0
 
     def frame(self, spp_per_rank: int, max_depth: int, stream: int) -> int:
         """One frame of spp_per_rank * world samples per pixel; returns kernels launched on this rank."""
         m = self.m
-        m.render_device(spp_per_rank, self.rank * spp_per_rank, max_depth, None, self.sum, stream)
-        self.dist.barrier()  # every rank's partial sums are complete in its HBM
-        m.reduce_tonemap_device(self.peer_sums, spp_per_rank * self.world, self.stripe[0], self.stripe[1],
+        self.epoch += 1
+        e, b, n = self.epoch, self.epoch & 1, 5
+        if e > 2:
+            m.flag_wait_device(self.done, e - 2, stream)
+            n += 1
+        m.render_device(spp_per_rank, self.rank * spp_per_rank, max_depth, None, self.sums[b], stream)
+        m.flag_set_device(self.ready[self.rank], e, stream)
+        m.flag_wait_device(self.ready, e, stream)
+        m.reduce_tonemap_device(self.peer_sums[b], spp_per_rank * self.world, self.stripe[0], self.stripe[1],
                                 self.rgb0, None, stream)
-        self.dist.barrier()  # rank 0's frame is complete
-        return 2
+        m.flag_set_device(self.done[self.rank], e, stream)
+        if self.rank == 0:
+            m.flag_wait_device(self.done, e, stream)
+            n += 1
+        return n
 
 
 class TileExchange:
     """Tile-interleaved split over peer memory: rank 0 exports its RGB8 frame through CUDA IPC, every rank
-    renders its own tiles (all samples) straight into it.  One trace launch per rank and frame, no reduce."""
+    renders its own tiles (all samples) straight into it.  One trace launch per rank and frame, no reduce, and no
+    host-side barrier: frame e is ordered by two flags in peer-visible memory,
+        rank 0: set go = e            everything rank 0 queued before (the caller's copy of frame e - 1) is complete
+        all:    wait rank 0's go >= e
+        render own tiles -> rank 0's frame
+        set my done = e
+        rank 0: wait peers' done >= e the frame is complete in rank 0's memory."""
 
-    mode = "tile-interleaved (32x4 tiles), RGB8 stored into rank 0's frame over NVLink (CUDA IPC)"
+    mode = "tile-interleaved (32x4 tiles), RGB8 stored into rank 0's frame over NVLink (CUDA IPC), flag-ordered"
 
     def __init__(self, model, dist, device):
         import ctypes
@@ -105,15 +143,31 @@ class TileExchange:
         self.m, self.dist = model, dist
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
         self.npix = model.width * model.height
-        q = ctypes.c_void_p()
-        _lib.check(_lib.lib().forma_rt_device_alloc(model._h, self.npix * 3, ctypes.byref(q)))
-        self.rgb = q.value
-        handles = gather_bytes(dist, model.ipc_export(self.rgb), device)
-        self.rgb0 = self.rgb if self.rank == 0 else model.ipc_open(handles[0])
+
+        def alloc(nbytes):
+            q = ctypes.c_void_p()
+            _lib.check(_lib.lib().forma_rt_device_alloc(model._h, nbytes, ctypes.byref(q)))  # zero-filled
+            return q.value
+
+        self.rgb = alloc(self.npix * 3)
+        self.flags = alloc(256)  # done at +0, go (rank 0's) at +128
+        handles = gather_bytes(dist, model.ipc_export(self.rgb) + model.ipc_export(self.flags), device)
+        self.rgb0 = self.rgb if self.rank == 0 else model.ipc_open(handles[0][:64])
+        peer_flags = [self.flags if r == self.rank else model.ipc_open(handles[r][64:]) for r in range(self.world)]
+        self.done = peer_flags
+        self.go = peer_flags[0] + 128
+        self.epoch = 0
         model.set_partition(self.rank, self.world)
 
     def frame(self, spp: int, max_depth: int, stream: int) -> int:
-        self.m.render_device(spp, 0, max_depth, self.rgb0, None, stream)
-        self.dist.barrier()  # stream-ordered (NCCL on the launch stream): rank 0's frame is complete
+        m = self.m
+        self.epoch += 1
+        e = self.epoch
+        if self.rank == 0:
+            m.flag_set_device(self.go, e, stream)
+        m.flag_wait_device([self.go], e, stream)
+        m.render_device(spp, 0, max_depth, self.rgb0, None, stream)
+        m.flag_set_device(self.done[self.rank], e, stream)
+        if self.rank == 0:
+            m.flag_wait_device(self.done, e, stream)
         return 1
-

@@ -224,6 +224,15 @@ class TraceModel:
         check(_lib.lib().forma_rt_reduce_tonemap_device(self._h, arr, len(peer_ptrs), spp_total, pixel_begin, pixel_end,
                                                         d_rgb, d_sum_out, stream or None))
 
+    def flag_set_device(self, d_flag: int, value: int, stream: int = 0):
+        """*d_flag = value once everything queued on `stream` so far is complete and visible system-wide."""
+        check(_lib.lib().forma_rt_flag_set_device(self._h, d_flag, value & 0xFFFFFFFF, stream or None))
+
+    def flag_wait_device(self, d_flags, value: int, stream: int = 0):
+        """Later work on `stream` starts once every flag in d_flags has reached `value`."""
+        arr = (ctypes.c_void_p * len(d_flags))(*d_flags)
+        check(_lib.lib().forma_rt_flag_wait_device(self._h, arr, len(d_flags), value & 0xFFFFFFFF, stream or None))
+
     def ipc_export(self, d_ptr: int) -> bytes:
         buf = (ctypes.c_uint8 * 64)()
         check(_lib.lib().forma_rt_ipc_export(self._h, d_ptr, buf))

@@ -205,11 +205,20 @@ FORMA_RT_API int forma_rt_reduce_tonemap_device(forma_rt* ctx, const void* const
                                    void* d_sum_out, void* stream);
 /* CUDA IPC plumbing for the above: export a handle (64 bytes) of a device allocation of this
  * process, open a peer's handle, close it. */
+/* Stream-ordered flags in peer-visible device memory (added): how the sample-split exchange orders its kernels
+ * across GPUs without host-side barriers.  A flag is a zero-initialised uint32 in a forma_rt_device_alloc'ed buffer that
+ * the peers map through forma_rt_ipc_open.  set: once everything queued on `stream` before the call is complete and
+ * visible system-wide, *d_flag = value.  wait: work queued on `stream` after the call starts only when every
+ * *d_flags[i] has reached `value` (n <= 16; values only grow; comparison is wrap-safe). */
+FORMA_RT_API int forma_rt_flag_set_device(forma_rt* ctx, void* d_flag, uint32_t value, void* stream);
+FORMA_RT_API int forma_rt_flag_wait_device(forma_rt* ctx, const void* const* d_flags, uint32_t n, uint32_t value,
+                                           void* stream);
+
 FORMA_RT_API int forma_rt_ipc_export(forma_rt* ctx, void* d_ptr, uint8_t handle[64]);
 FORMA_RT_API int forma_rt_ipc_open(forma_rt* ctx, const uint8_t handle[64], void** d_ptr);
 FORMA_RT_API int forma_rt_ipc_close(forma_rt* ctx, void* d_ptr);
 /* scratch device allocations owned by the handle (freed by forma_rt_destroy) */
-FORMA_RT_API int forma_rt_device_alloc(forma_rt* ctx, size_t bytes, void** d_ptr);
+FORMA_RT_API int forma_rt_device_alloc(forma_rt* ctx, size_t bytes, void** d_ptr); /* zero-filled */
 FORMA_RT_API int forma_rt_device_free(forma_rt* ctx, void* d_ptr);
 FORMA_RT_API int forma_rt_synchronize(forma_rt* ctx);
 

@@ -135,3 +135,42 @@ def test_tile_interleaved_partition_is_bit_exact():
             assert rays == rays_w and paths == w * h * spp
             assert np.array_equal(rgb.cpu().numpy(), rgb_w)
             assert np.array_equal(bits(lin.cpu().numpy()), bits(lin_w))
+
+
+def test_stream_ordered_flags():
+    """forma_rt_flag_set_device / forma_rt_flag_wait_device: a wait queued on one stream holds back the work behind
+    it until another stream raises the flag (the ordering the multi-GPU exchange relies on, here on one device)."""
+    import ctypes
+    import torch
+    from forma_b200 import _lib
+    m = forma_b200.create_model(64, 48, seed=0)
+    p = ctypes.c_void_p()
+    _lib.check(_lib.lib().forma_rt_device_alloc(m._h, 256, ctypes.byref(p)))
+    flag_a, flag_b = p.value, p.value + 128
+    dev = torch.device("cuda:0")
+    s1, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    marker = torch.zeros(1, dtype=torch.int32, device=dev)
+    # already satisfied: 0 >= 0, then set 5 and wait for 5 on the same stream
+    m.flag_wait_device([flag_a, flag_b], 0, s1.cuda_stream)
+    m.flag_set_device(flag_a, 5, s1.cuda_stream)
+    m.flag_wait_device([flag_a], 5, s1.cuda_stream)
+    s1.synchronize()
+    # s1 waits for flag_b >= 7, then writes the marker; s2 raises flag_b only after we have looked at the marker
+    m.flag_wait_device([flag_b], 7, s1.cuda_stream)
+    with torch.cuda.stream(s1):
+        marker.fill_(1)
+    import time
+    time.sleep(0.2)
+    assert not s1.query()                      # still held back by the wait
+    m.flag_set_device(flag_b, 6, s2.cuda_stream)  # not enough
+    s2.synchronize()
+    time.sleep(0.1)
+    assert not s1.query()
+    m.flag_set_device(flag_b, 7, s2.cuda_stream)
+    s2.synchronize()
+    s1.synchronize()
+    assert int(marker.item()) == 1
+    with pytest.raises(forma_b200.tracer.FormaError):
+        m.flag_wait_device([], 1)
+    with pytest.raises(forma_b200.tracer.FormaError):
+        m.flag_set_device(flag_a + 1, 1)
