@@ -259,6 +259,9 @@ def run_ours(args):
             else:
                 step()
                 if rank == 0:
+                    # rank 0's stream ends with the wait for every peer's part of the frame; the copy below runs on
+                    # the legacy default stream, which does not order itself behind torch's non-blocking streams
+                    ts.synchronize()
                     src = ex.rgb0 if ex else d_rgb.data_ptr()
                     _d2h(hp, src, npix * 3)
         for _ in range(2):
@@ -277,7 +280,9 @@ def run_ours(args):
         e2e = {"value": round(rays_step * args.steps / float(dt.item()) / 1e6, 1), "unit": UNIT,
                "ms_per_step": round(1e3 * float(dt.item()) / args.steps, 3),
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": npix * 3 + 8,
-               "api": "forma_rt_load_json + forma_rt_camera_json + forma_rt_render (host RGB8 buffer, pinned)"}
+               "api": "forma_rt_load_json + forma_rt_camera_json + forma_rt_render (host RGB8 buffer, pinned)" if world == 1 else
+                      "forma_rt_load_json + forma_rt_camera_json + forma_rt_render_device + flag-ordered exchange on every "
+                      "rank, then rank 0 waits for the frame and copies it to a pinned host RGB8 buffer"}
 
     others = None
     if world == 1 and not args.no_other_configs:
