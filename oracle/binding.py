@@ -15,7 +15,7 @@ from .scene_oracle import OBJECT_DTYPE
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "liboracle.so")
 
-FLAG_NO_JITTER, FLAG_PINHOLE, FLAG_SEQ_RNG = 1, 2, 4
+FLAG_NO_JITTER, FLAG_PINHOLE, FLAG_SEQ_RNG, FLAG_MT_ROWS = 1, 2, 4, 8
 CAMERA_FLOATS = 26
 # field offsets (in floats) inside the 26-float camera block
 CAM_FIELDS = {
@@ -170,3 +170,21 @@ def tonemap(linear_sum: np.ndarray, spp: int) -> np.ndarray:
     rgb = np.zeros(lin.shape, dtype=np.uint8)
     lib().oracle_tonemap(lin.ctypes.data, npix, spp, rgb.ctypes.data)
     return rgb
+
+
+def render_mt(cam: np.ndarray, w: int, h: int, frame: int = 0, seed: int = 0) -> np.ndarray:
+    """tracer::render_mt (tracer.rs:83-134): one 1-spp frame of a FRESH get_simple_scene() (:105 - not the model's
+    scene) through the model's camera, in four bands; returns the (4 * (h // 4), w, 3) u8 rows it produces."""
+    rgb, _, _ = render(builtin_scene(0), cam, w, h, 1, sample_offset=frame, seed=seed, flags=FLAG_MT_ROWS,
+                       want_linear=False)
+    return rgb[:4 * (h // 4)]
+
+
+def save_image_mt(cam: np.ndarray, w: int, h: int, sample: int, seed: int = 0) -> np.ndarray:
+    """tracer::save_image_mt's loops (tracer.rs:139-154): the u8 frames of `sample` render_mt calls averaged AFTER
+    gamma in f32 (acc += p as f32 / sample as f32), `as u8`; rows render_mt does not produce stay 0."""
+    acc = np.zeros((h, w, 3), dtype=np.float32)
+    for k in range(sample):
+        f = render_mt(cam, w, h, k, seed)
+        acc[:f.shape[0]] = acc[:f.shape[0]] + f.astype(np.float32) / np.float32(sample)
+    return np.minimum(acc, np.float32(255.0)).astype(np.uint8)

@@ -535,7 +535,7 @@ inline uint8_t as_u8(float f) {
     return (uint8_t)(int)f;
 }
 
-enum : uint32_t { FLAG_NO_JITTER = 1, FLAG_PINHOLE = 2, FLAG_SEQ_RNG = 4 };
+enum : uint32_t { FLAG_NO_JITTER = 1, FLAG_PINHOLE = 2, FLAG_SEQ_RNG = 4, FLAG_MT_ROWS = 8 };
 
 }  // namespace
 
@@ -708,6 +708,17 @@ uint64_t oracle_render(const Object* objs, uint64_t n, const Camera* cam, uint32
                     else { float r[4]; ctx.block(0, r); xi_u = r[0]; xi_v = r[1]; }
                     float u = ((float)x + xi_u) / (float)width;                 // tracer.rs:171
                     float v = ((float)(height - y) + xi_v) / (float)height;     // tracer.rs:172 (Q1)
+                    if (flags & FLAG_MT_ROWS) {
+                        // render_mt (tracer.rs:83-134): four bands of t_height = height / 4 rows, each traced by its
+                        // own thread with v = ((t_height - y) + xi) / height + t_id / 4 (:99-103), the bands appended
+                        // in DESCENDING t_id (:126-131): output row y is row y % t_height of band 3 - y / t_height.
+                        // Rows past 4 * t_height do not exist in its result (left zero here).
+                        const uint32_t t_height = height / 4;
+                        if (y >= 4 * t_height) continue;
+                        const uint32_t t_id = 3 - y / t_height, yb = y % t_height;
+                        v = ((float)(t_height - yb) + xi_v) / (float)height;
+                        v += (float)t_id * (1.0f / 4.0f);
+                    }
                     Ray ray = camera_get_ray(*cam, u, v, (flags & FLAG_PINHOLE) != 0);
                     col = col + get_color(ray, tr, 0);                          // tracer.rs:174
                 }
