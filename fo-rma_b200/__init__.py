@@ -3,6 +3,6 @@
 `tracer` mirrors the reference's Rust module over it.  Import name: `forma_b200` (the directory
 is called fo-rma_b200; forma_b200.py at the repo root aliases it)."""
 from . import _lib, tracer  # noqa: F401
-from .tracer import TraceModel, create_model, save_image, srgb_table, update, update_progressive  # noqa: F401
+from .tracer import TraceModel, create_model, save_image, save_image_mt, srgb_table, update, update_progressive  # noqa: F401
 
-__all__ = ["tracer", "TraceModel", "create_model", "update", "update_progressive", "save_image", "srgb_table"]
+__all__ = ["tracer", "TraceModel", "create_model", "update", "update_progressive", "save_image", "save_image_mt", "srgb_table"]

@@ -86,6 +86,9 @@ SYMBOLS = {
     "forma_rt_render": (_int, [_vp, _u32, _u32, _u32, _vp, _vp]),
     "forma_rt_save_image": (_int, [_vp, _u32, ctypes.c_char_p]),
     "forma_rt_primary_hits": (_int, [_vp, _vp, _vp]),
+    "forma_rt_render_mt": (_int, [_vp, _u32, _vp]),
+    "forma_rt_render_mt_average": (_int, [_vp, _u32, _vp]),
+    "forma_rt_save_image_mt": (_int, [_vp, _u32, ctypes.c_char_p]),
     "forma_rt_render_device": (_int, [_vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "forma_rt_tonemap_device": (_int, [_vp, _vp, _u32, _u64, _u64, _vp, _vp]),
     "forma_rt_reduce_tonemap_device": (_int, [_vp, ctypes.POINTER(_vp), _u32, _u32, _u64, _u64, _vp, _vp, _vp]),

@@ -68,6 +68,8 @@ namespace forma {
 int set_last_error(int code, const std::string& msg) { return fail(code, msg); }
 }  // namespace forma
 
+extern "C" void forma_rt_destroy(forma_rt* ctx);
+
 struct forma_rt {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -84,6 +86,9 @@ struct forma_rt {
     uint32_t part_mod = 1, part_rem = 0;  // forma_rt_set_partition: this handle renders the 32x4 tiles t with t % part_mod == part_rem
     int fast_div = -1;   // div_const (trace.cuh): -1 not checked yet, 0 IEEE division, 1 verified multiply form
     uint32_t frame = 0;  // update() call counter -> sample index of the interactive frame
+    forma_rt* mt_scene = nullptr;  // render_mt traces a FRESH get_simple_scene() (tracer.rs:105): a child handle holds it
+    DevBuf<uint8_t> d_mt_frame;    // one render_mt frame
+    DevBuf<float> d_mt_acc;        // save_image_mt's pixels_acc
 
     // packed scene (host copies kept for re-upload after set_object)
     DevBuf<float4> d_spheres, d_tris, d_planes, d_material;
@@ -113,6 +118,7 @@ struct forma_rt {
     int sm_count = 0, clock_khz = 0;
 
     ~forma_rt() {
+        if (mt_scene) forma_rt_destroy(mt_scene);
         if (device < 0) return;  // host-only handle owns no device resources
         cudaSetDevice(device);
         if (stream) cudaStreamSynchronize(stream);
@@ -121,6 +127,7 @@ struct forma_rt {
         d_sphere_obj.release(); d_tri_obj.release(); d_plane_obj.release(); d_kindmat.release(); d_ids.release();
         d_segments.release(); d_rgb.release(); d_sum.release(); d_prim.release(); d_t.release();
         d_rad.release(); d_acc.release(); d_job.release(); d_prog.release(); d_walk.release();
+        d_mt_frame.release(); d_mt_acc.release();
         bvh.release();
         if (d_rays) cudaFree(d_rays);
         if (h_rays) cudaFreeHost(h_rays);
@@ -965,6 +972,105 @@ int forma_rt_write_png(const char* path, const uint8_t* rgb, uint32_t width, uin
     std::string err;
     if (!forma::write_png_rgb8(path, rgb, width, height, err)) return fail(FORMA_RT_EIO, err);
     return FORMA_RT_OK;
+}
+
+}  // extern "C"
+
+// ---- tracer::render_mt / save_image_mt (tracer.rs:83-158) --------------------------------------------------
+namespace {
+
+// one render_mt frame into c->d_mt_frame (width * 4 * (height / 4) * 3 bytes) on the handle's stream
+int render_mt_on_device(forma_rt* c, uint32_t frame) {
+    if (!c->mt_scene) {  // Scene::new's objects = get_simple_scene(), scanned (4 objects)
+        forma_rt_options o{};
+        o.struct_size = sizeof o;
+        o.device = c->device; o.seed = c->seed; o.accel = FORMA_RT_ACCEL_BRUTE;
+        int rc = forma_rt_create(&o, c->width, c->height, &c->mt_scene);
+        if (rc) return rc;
+    }
+    int rc = ensure_scene(c->mt_scene);
+    if (rc) return rc;
+    cudaSetDevice(c->device);
+    const size_t rows = 4 * (size_t)(c->height / 4);
+    CU_TRY(c->d_mt_frame.ensure(std::max<size_t>(1, rows * c->width * 3)));
+    forma::MtParams P{};
+    P.cam = c->scene.camera.c;
+    P.scene = c->mt_scene->view;
+    P.width = c->width; P.height = c->height; P.frame = frame; P.max_depth = 50;  // tracer.rs:10
+    P.rk.expand(c->seed);
+    P.rgb = c->d_mt_frame.p; P.rays = c->d_rays;
+    CU_TRY(forma::launch_render_mt(P, c->stream));
+    return FORMA_RT_OK;
+}
+
+int average_mt_to_host(forma_rt* c, uint32_t sample, uint8_t* rgb) {
+    if (sample == 0) return fail(FORMA_RT_EINVAL, "save_image_mt: sample must be >= 1");
+    const size_t n = (size_t)c->width * c->height * 3, n_mt = (size_t)c->width * 4 * (c->height / 4) * 3;
+    cudaStream_t s = c->stream;
+    CU_TRY(c->d_mt_acc.ensure(n));
+    CU_TRY(c->d_rgb.ensure(n));
+    CU_TRY(cudaMemsetAsync(c->d_mt_acc.p, 0, n * sizeof(float), s));  // tracer.rs:139: vec![0.0; w * h * 3]
+    CU_TRY(cudaMemsetAsync(c->d_rays, 0, sizeof(unsigned long long), s));
+    CU_TRY(cudaEventRecord(c->ev_begin, s));
+    CU_TRY(cudaEventRecord(c->ev_k0, s));
+    for (uint32_t k = 0; k < sample; ++k) {  // tracer.rs:140-145
+        if (int rc = render_mt_on_device(c, k)) return rc;
+        CU_TRY(forma::launch_mt_accumulate(c->d_mt_frame.p, c->d_mt_acc.p, sample, n_mt, c->sm_count, s));
+    }
+    CU_TRY(forma::launch_mt_finish(c->d_mt_acc.p, c->d_rgb.p, n, c->sm_count, s));  // tracer.rs:148-154
+    CU_TRY(cudaEventRecord(c->ev_k1, s));
+    CU_TRY(cudaMemcpyAsync(rgb, c->d_rgb.p, n, cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaMemcpyAsync(c->h_rays, c->d_rays, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaEventRecord(c->ev_end, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    c->stats.rays = *c->h_rays;
+    c->stats.paths = (uint64_t)c->width * 4 * (c->height / 4) * sample;
+    c->stats.gpu_launches = 2 * sample + 1;
+    c->stats_pending = false;
+    CU_TRY(cudaEventElapsedTime(&c->stats.kernel_ms, c->ev_k0, c->ev_k1));
+    CU_TRY(cudaEventElapsedTime(&c->stats.total_ms, c->ev_begin, c->ev_end));
+    return FORMA_RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int forma_rt_render_mt(forma_rt* ctx, uint32_t frame, uint8_t* rgb) {
+    NEED_DEV(ctx);
+    if (!rgb) return fail(FORMA_RT_EINVAL, "forma_rt_render_mt: rgb is null");
+    cudaStream_t s = ctx->stream;
+    const size_t n_mt = (size_t)ctx->width * 4 * (ctx->height / 4) * 3;
+    CU_TRY(cudaMemsetAsync(ctx->d_rays, 0, sizeof(unsigned long long), s));
+    CU_TRY(cudaEventRecord(ctx->ev_begin, s));
+    CU_TRY(cudaEventRecord(ctx->ev_k0, s));
+    if (int rc = render_mt_on_device(ctx, frame)) return rc;
+    CU_TRY(cudaEventRecord(ctx->ev_k1, s));
+    if (n_mt) CU_TRY(cudaMemcpyAsync(rgb, ctx->d_mt_frame.p, n_mt, cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaMemcpyAsync(ctx->h_rays, ctx->d_rays, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaEventRecord(ctx->ev_end, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    ctx->stats.rays = *ctx->h_rays;
+    ctx->stats.paths = (uint64_t)ctx->width * 4 * (ctx->height / 4);
+    ctx->stats.gpu_launches = n_mt ? 1 : 0;
+    ctx->stats_pending = false;
+    CU_TRY(cudaEventElapsedTime(&ctx->stats.kernel_ms, ctx->ev_k0, ctx->ev_k1));
+    CU_TRY(cudaEventElapsedTime(&ctx->stats.total_ms, ctx->ev_begin, ctx->ev_end));
+    return FORMA_RT_OK;
+}
+
+int forma_rt_render_mt_average(forma_rt* ctx, uint32_t sample, uint8_t* rgb) {
+    NEED_DEV(ctx);
+    if (!rgb) return fail(FORMA_RT_EINVAL, "forma_rt_render_mt_average: rgb is null");
+    return average_mt_to_host(ctx, sample, rgb);
+}
+
+int forma_rt_save_image_mt(forma_rt* ctx, uint32_t sample, const char* path) {
+    NEED_DEV(ctx);
+    if (!path) return fail(FORMA_RT_EINVAL, "forma_rt_save_image_mt: path is null");
+    std::vector<uint8_t> rgb((size_t)ctx->width * ctx->height * 3);
+    if (int rc = average_mt_to_host(ctx, sample, rgb.data())) return rc;
+    return forma_rt_write_png(path, rgb.data(), ctx->width, ctx->height);
 }
 
 }  // extern "C"

@@ -102,6 +102,16 @@ struct RenderParams {
                                         // instrumented instantiation of render_tree_kernel; forma_rt_walk_stats)
 };
 
+// tracer::render_mt (tracer.rs:83-134): one 1-spp frame in four bands (kernels.cu render_mt_kernel)
+struct MtParams {
+    forma_rt_camera cam;       // the model's camera (tracer.rs:90 clones it)
+    SceneView scene;           // a fresh get_simple_scene() (tracer.rs:105), never the model's scene
+    uint32_t width, height, frame, max_depth;
+    RoundKeys rk;
+    uint8_t* rgb;              // width * 4 * (height / 4) * 3 bytes
+    unsigned long long* rays;
+};
+
 struct PrimaryParams {
     forma_rt_camera cam;
     SceneView scene;

@@ -414,6 +414,63 @@ __global__ void accumulate_kernel(const __grid_constant__ RenderParams P, int fi
     }
 }
 
+// tracer::render_mt (tracer.rs:83-134): four bands of t_height = height / 4 rows, each traced by
+// its own thread in the reference, v = ((t_height - y) + xi) / height + t_id / 4 (:99-103), one sample per pixel, sqrt
+// gamma and `as u8` per sample (:107-112); the bands are appended in DESCENDING t_id (:126-131), so output row r is row
+// r % t_height of band 3 - r / t_height.  Rows past 4 * t_height do not exist in its result.  One thread per pixel;
+// the path is get_color (tracer.rs:189-219) unrolled into a loop with the attenuations multiplied innermost first.
+__global__ void __launch_bounds__(kBlock) render_mt_kernel(const __grid_constant__ MtParams P) {
+    const SceneView& S = P.scene;
+    const float4 *sph = S.spheres, *tri = S.tris;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t x = blockIdx.x * kTileW + warp * 8 + (lane & 7), r = blockIdx.y * kTileH + (lane >> 3);
+    const uint32_t t_height = P.height / 4u;
+    uint32_t rays = 0;
+    if (x < P.width && r < 4u * t_height) {
+        const uint32_t t_id = 3u - r / t_height, yb = r % t_height;
+        PathRng rng{P.rk, x + r * P.width, P.frame};
+        const Rand4 r0 = rng.block(0, 0);
+        const float u = ((float)x + r0.x) / (float)P.width;                    // tracer.rs:99
+        float v = ((float)(t_height - yb) + r0.y) / (float)P.height;           // tracer.rs:100
+        v += (float)t_id * (1.0f / 4.0f);                                      // tracer.rs:101
+        float3 o, d;
+        camera_ray(P.cam, rng, r0, u, v, false, o, d);                         // tracer.rs:102
+        int astack[kMaxDepthCap];
+        uint32_t depth = 0;
+        float3 pc = f3(0.0f, 0.0f, 0.0f);
+        for (;;) {                                                             // tracer.rs:103 get_color(ray, scene, 0)
+            HitState h;
+            closest_hit<kScanGlobal>(S, sph, tri, o, d, h);
+            ++rays;
+            if (h.obj < 0) { pc = sky(d); break; }
+            float3 no, nd;
+            if (depth < P.max_depth && scatter(S, rng, 1u + depth, d, h, no, nd)) {
+                astack[depth++] = h.obj;
+                o = no; d = nd;
+                continue;
+            }
+            break;  // black
+        }
+        while (depth > 0) { --depth; pc = attenuation(S, astack[depth]) * pc; }
+        uint8_t* px = P.rgb + ((size_t)x + (size_t)r * P.width) * 3;
+        px[0] = (uint8_t)as_u8(sqrtf(pc.x) * 255.0f);                          // tracer.rs:107-112
+        px[1] = (uint8_t)as_u8(sqrtf(pc.y) * 255.0f);
+        px[2] = (uint8_t)as_u8(sqrtf(pc.z) * 255.0f);
+    }
+    const uint32_t wr = __reduce_add_sync(0xffffffffu, rays);
+    if (lane == 0 && wr) atomicAdd(P.rays, (unsigned long long)wr);
+}
+
+// tracer::save_image_mt (tracer.rs:139-154): acc[i] += pixels[i] as f32 / sample as f32, then acc[i] as u8
+__global__ void mt_accumulate_kernel(const uint8_t* __restrict__ frame, float* __restrict__ acc, float sample, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        acc[i] = acc[i] + (float)frame[i] / sample;
+}
+__global__ void mt_finish_kernel(const float* __restrict__ acc, uint8_t* __restrict__ out, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = (uint8_t)as_u8(acc[i]);
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(kBlock) primary_hits_kernel(const __grid_constant__ PrimaryParams P) {
     const float4 *sph, *tri;
@@ -643,6 +700,26 @@ cudaError_t launch_reduce_tonemap(const float4* const* peers, int n_peers, uint3
     for (int i = 0; i < n_peers; ++i) pp.p[i] = peers[i];
     reduce_tonemap_kernel<<<stream_grid(end - begin, sm_count), 256, 0, stream>>>(pp, n_peers, (float)spp, begin, end,
                                                                                   rgb, sum_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_render_mt(const MtParams& P, cudaStream_t stream) {
+    if (P.height / 4u == 0u) return cudaSuccess;  // t_height = 0: render_mt returns an empty Vec
+    const dim3 grid((P.width + kTileW - 1) / kTileW, (4u * (P.height / 4u) + kTileH - 1) / kTileH);
+    render_mt_kernel<<<grid, kBlock, 0, stream>>>(P);
+    return cudaGetLastError();
+}
+
+static int stream_grid(uint64_t n, int sm_count);
+cudaError_t launch_mt_accumulate(const uint8_t* frame, float* acc, uint32_t sample, size_t n, int sm_count, cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    mt_accumulate_kernel<<<stream_grid(n, sm_count), 256, 0, stream>>>(frame, acc, (float)sample, n);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_mt_finish(const float* acc, uint8_t* out, size_t n, int sm_count, cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    mt_finish_kernel<<<stream_grid(n, sm_count), 256, 0, stream>>>(acc, out, n);
     return cudaGetLastError();
 }
 

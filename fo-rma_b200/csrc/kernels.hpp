@@ -23,6 +23,10 @@ cudaError_t launch_reduce_tonemap(const float4* const* peers, int n_peers, uint3
 cudaError_t launch_l2_read(const void* buf, size_t bytes, uint32_t passes, uint32_t* sink, int sm_count, cudaStream_t stream,
                            size_t* bytes_per_pass);
 
+// tracer::render_mt / save_image_mt (tracer.rs:83-158)
+cudaError_t launch_render_mt(const MtParams& P, cudaStream_t stream);
+cudaError_t launch_mt_accumulate(const uint8_t* frame, float* acc, uint32_t sample, size_t n, int sm_count, cudaStream_t stream);
+cudaError_t launch_mt_finish(const float* acc, uint8_t* out, size_t n, int sm_count, cudaStream_t stream);
 // stream-ordered flags in peer-visible memory (kernels.cu): *flag = value after everything earlier on `stream` is visible
 // system-wide; later work on `stream` starts once every *flags[i] has reached value (n <= 16)
 cudaError_t launch_flag_set(uint32_t* flag, uint32_t value, cudaStream_t stream);

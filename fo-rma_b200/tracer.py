@@ -193,6 +193,20 @@ class TraceModel:
         """color_utils::srgb_encode (color_utils.rs:49-66) in place on a device RGB8 buffer."""
         check(_lib.lib().forma_rt_srgb_encode_device(self._h, d_rgb, nbytes, stream or None))
 
+    def render_mt(self, frame: int = 0) -> np.ndarray:
+        """tracer::render_mt (tracer.rs:83-134): the (4 * (h // 4), w, 3) u8 rows of one banded 1-spp frame of a fresh
+        get_simple_scene() through this model's camera."""
+        out = np.zeros((4 * (self.height // 4), self.width, 3), dtype=np.uint8)
+        buf = out if out.size else np.zeros(1, np.uint8)
+        check(_lib.lib().forma_rt_render_mt(self._h, frame, buf.ctypes.data))
+        return out
+
+    def render_mt_average(self, sample: int) -> np.ndarray:
+        """save_image_mt's loops (tracer.rs:139-154) without the PNG: (h, w, 3) u8."""
+        out = np.empty((self.height, self.width, 3), dtype=np.uint8)
+        check(_lib.lib().forma_rt_render_mt_average(self._h, sample, out.ctypes.data))
+        return out
+
     def primary_hits(self):
         ids = np.empty((self.height, self.width), dtype=np.int32)
         ts = np.empty((self.height, self.width), dtype=np.float32)
@@ -278,6 +292,11 @@ def srgb_table() -> np.ndarray:
     t = np.zeros(256, dtype=np.uint8)
     check(_lib.lib().forma_rt_srgb_table(t.ctypes.data))
     return t
+
+
+def save_image_mt(model: TraceModel, sample: int, path: str = "out/basic_mt.png") -> None:
+    """tracer::save_image_mt (tracer.rs:136-158).  Raises FormaError(EIO) where the reference panics."""
+    check(_lib.lib().forma_rt_save_image_mt(model._h, sample, os.fsencode(path)))
 
 
 def save_image(model: TraceModel, sample: int, path: str = "out/basic.png") -> None:

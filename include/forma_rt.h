@@ -175,6 +175,18 @@ FORMA_RT_API int forma_rt_render(forma_rt* ctx, uint32_t spp, uint32_t sample_of
 /* tracer::save_image (tracer.rs:160-187): forma_rt_render + PNG to `path` ("out/basic.png" in the
  * reference).  Fails with FORMA_RT_EIO where the reference panics. */
 FORMA_RT_API int forma_rt_save_image(forma_rt* ctx, uint32_t sample, const char* path);
+/* tracer::render_mt (tracer.rs:83-134), the 4-thread variant `update` has commented out (tracer.rs:53): one 1-spp
+ * frame in four bands of height / 4 rows - v = ((t_height - y) + xi) / height + t_id / 4, bands appended in descending
+ * t_id - of a FRESH get_simple_scene() (tracer.rs:105: not the model's scene, whatever it holds) through the model's
+ * camera, sqrt gamma and `as u8` per sample.  rgb receives what its Vec holds: width * 4 * (height / 4) * 3 bytes
+ * (nothing when height < 4).  `frame` is the sample index of the counter RNG.
+ * forma_rt_render_mt_average is tracer::save_image_mt's loops (tracer.rs:139-154): frames 0 .. sample-1 averaged
+ * AFTER gamma in f32 (acc += p as f32 / sample as f32), `as u8`, into a full width * height * 3 frame whose rows past
+ * 4 * (height / 4) stay 0; forma_rt_save_image_mt writes that frame as a PNG ("out/basic_mt.png" in the reference)
+ * and fails with FORMA_RT_EIO where the reference panics. */
+FORMA_RT_API int forma_rt_render_mt(forma_rt* ctx, uint32_t frame, uint8_t* rgb);
+FORMA_RT_API int forma_rt_render_mt_average(forma_rt* ctx, uint32_t sample, uint8_t* rgb);
+FORMA_RT_API int forma_rt_save_image_mt(forma_rt* ctx, uint32_t sample, const char* path);
 /* primary-ray dump (added; config B): xi = 0.5, pinhole.  prim_id[width*height] = object id of the
  * closest hit or -1; t[width*height] = its distance (FLT_MAX on a miss). */
 FORMA_RT_API int forma_rt_primary_hits(forma_rt* ctx, int32_t* prim_id, float* t);

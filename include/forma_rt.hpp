@@ -13,6 +13,7 @@
 //   forma::tracer::create_model(width, height)                tracer.rs:19-28
 //   forma::tracer::update(model, keys, delta_time)            tracer.rs:30-55
 //   forma::tracer::save_image(model, sample)                  tracer.rs:160-187 (writes out/basic.png)
+//   forma::tracer::save_image_mt(model, sample)               tracer.rs:136-158 (writes out/basic_mt.png)
 //   forma::scene_loader::construct_scene_from_json(model, s)  basics/scene_loader.rs:3-7 (+ the RT mapping)
 #ifndef FORMA_RT_HPP
 #define FORMA_RT_HPP
@@ -135,6 +136,11 @@ inline void update(TraceModel& model, uint8_t keys, float delta_time) {
 // panics (tracer.rs:186 `unwrap`, e.g. ./out missing)
 inline void save_image(const TraceModel& model, uint32_t sample, const char* path = "out/basic.png") {
     check(forma_rt_save_image(model.handle(), sample, path));
+}
+
+// tracer.rs:136-158: the 4-band variant, written to out/basic_mt.png (a fresh get_simple_scene(), post-gamma average)
+inline void save_image_mt(const TraceModel& model, uint32_t sample, const char* path = "out/basic_mt.png") {
+    check(forma_rt_save_image_mt(model.handle(), sample, path));
 }
 
 // save_image's loops without the PNG (added): the sqrt-gamma RGB8 frame of `sample` samples per pixel
