@@ -120,7 +120,7 @@ struct FrameConst {
 namespace rt1 {
 constexpr float EPSILON = 4e-4f;  // rt.wgsl:7
 constexpr int SAMPLES = 1000;     // rt.wgsl:8
-constexpr int kGroupTail = 8;     // a warp with at most this many live paths finishes them on 4-lane groups
+constexpr int kGroupTail = 4;     // a warp with at most this many live paths finishes them on 8-lane groups
 
 // Hit (rt.wgsl:25-29); material = (color, f0), f0 < 0 = no hit
 struct Hit { float t; V3 normal; V3 color; float f0; };
@@ -245,16 +245,18 @@ __device__ __forceinline__ bool trip(Path& p, const FrameConst& fc, uint32_t& ra
 
 // The tail.  rt.wgsl's loop runs up to 1000 trips and the frame holds pixels that use them all: one dependent chain
 // per trip (query -> normal -> mirror ray) on a lane whose 31 neighbours have long finished.  Once a warp is down to
-// <= kGroupTail live paths, each path moves to a group of 4 lanes.  Lane k of the group tests primitive k (plane, s1,
-// s2, s3) of the primary query and the group takes the minimum (ties to the earlier primitive, as the sequential
-// `compare` of rt.wgsl:77-85 does); every lane of the group keeps the whole path state.  The loop is software-
-// pipelined: the next ray needs only the hit, not its light, so trip k's primary query and trip k-1's shadow query
-// (lane k tests primitive k again, a ballot ORs them) sit in one basic block and their chains interleave; the light of
-// trip k-1 is added before anything trip k adds, so every sum sees its terms in the shader's order.  Same operations
-// on the same values - bit-identical - on a much shorter critical path.
+// <= kGroupTail live paths, each path moves to a group of 8 lanes, every one of which keeps the whole path state.
+// The loop is software-pipelined - the next ray needs only the hit, not its light - so trip k's primary query and trip
+// k-1's shadow query are independent, and they run SIDE BY SIDE: lane k of the group's first quad tests primitive k
+// (plane, s1, s2, s3) against the ray, lane k of its second quad tests primitive k against the previous hit's shadow
+// ray - one pass through the test code for both.  The first quad takes the minimum (ties to the earlier primitive, as
+// the sequential `compare` of rt.wgsl:77-85 does) and hands it to the second; a ballot ORs the shadow tests.  The
+// light of trip k-1 is added before anything trip k adds, so every sum sees its terms in the shader's order.  Same
+// operations on the same values - bit-identical - on a much shorter critical path.
 __device__ __forceinline__ void finish_in_groups(unsigned live, bool& alive, Path& p, const FrameConst& fc, uint32_t& rays) {
     const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x & 31, g = lane >> 2, sub = lane & 3;
+    const int lane = threadIdx.x & 31, g = lane >> 3, sub = lane & 3;
+    const bool shadow_quad = (lane & 4) != 0;
     const bool has = g < __popc(live);
     const int src = has ? (int)__fns(live, 0, g + 1) : lane;  // the g-th live lane
     Path q;
@@ -264,31 +266,34 @@ __device__ __forceinline__ void finish_in_groups(unsigned live, bool& alive, Pat
     q.attenuation = v3(__shfl_sync(full, p.attenuation.x, src), __shfl_sync(full, p.attenuation.y, src), __shfl_sync(full, p.attenuation.z, src));
     q.i = __shfl_sync(full, p.i, src);
     const float inf = __uint_as_float(0x7f800000u);
-    const V3 center = v3((float)(2 * sub - 4), 1.0f, 0.0f);  // of sphere `sub` (1..3); lane 0 of a group has the plane
+    const V3 center = v3((float)(2 * sub - 4), 1.0f, 0.0f);  // of sphere `sub` (1..3); lane 0 of a quad has the plane
     bool galive = has, pending = false;  // pending: the previous trip's hit still waits for its light
     Hit ph = surface(-1, 1e10f, q.ray);
     V3 pdir = q.ray.direction;
     Ray psr = Ray{q.ray.origin, fc.sun_light};
     while (__any_sync(full, galive || pending)) {
-        float tp, ts, stp, sts;
-        const bool okp = plane_t(1e10f, q.ray, tp), oks = sphere_t(1e10f, q.ray, center, ts);
-        const bool sokp = plane_t(1e10f, psr, stp), soks = sphere_t(1e10f, psr, center, sts);
-        float t = (sub == 0 ? okp : oks) ? (sub == 0 ? tp : ts) : inf;
+        const Ray tr = shadow_quad ? psr : q.ray;
+        float tp, ts;
+        const bool okp = plane_t(1e10f, tr, tp), oks = sphere_t(1e10f, tr, center, ts);
+        const bool ok = sub == 0 ? okp : oks;
+        float t = ok ? (sub == 0 ? tp : ts) : inf;
         int which = sub;
 #pragma unroll
-        for (int m = 1; m <= 2; m <<= 1) {
+        for (int m = 1; m <= 2; m <<= 1) {  // within each quad
             const float ot = __shfl_xor_sync(full, t, m);
             const int ow = __shfl_xor_sync(full, which, m);
             if (ot < t || (ot == t && ow < which)) { t = ot; which = ow; }
         }
-        const unsigned shadow_bits = __ballot_sync(full, pending && (sub == 0 ? sokp : soks));
+        t = __shfl_sync(full, t, lane & ~4);          // the primary quad's result, for all eight lanes
+        which = __shfl_sync(full, which, lane & ~4);
+        const unsigned shadow_bits = __ballot_sync(full, shadow_quad && pending && ok);
         if (pending) {
-            shade(q, ph, pdir, ((shadow_bits >> (g * 4)) & 15u) != 0u, fc);
+            shade(q, ph, pdir, ((shadow_bits >> (g * 8 + 4)) & 15u) != 0u, fc);
             pending = false;
         }
         if (galive) {
             const bool is_hit = t < inf;
-            if (sub == 0) rays += is_hit ? 2u : 1u;
+            if ((lane & 7) == 0) rays += is_hit ? 2u : 1u;
             if (is_hit) {
                 ph = surface(which, t, q.ray);
                 pdir = q.ray.direction;
@@ -303,7 +308,7 @@ __device__ __forceinline__ void finish_in_groups(unsigned live, bool& alive, Pat
         }
     }
     // the r-th live lane's path ran on group r
-    const int back = alive ? 4 * __popc(live & ((1u << lane) - 1u)) : lane;
+    const int back = alive ? 8 * __popc(live & ((1u << lane) - 1u)) : lane;
     const V3 done = v3(__shfl_sync(full, q.accum.x, back), __shfl_sync(full, q.accum.y, back), __shfl_sync(full, q.accum.z, back));
     if (alive) p.accum = done;
     alive = false;
