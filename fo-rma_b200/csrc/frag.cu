@@ -153,6 +153,19 @@ __device__ __forceinline__ bool sphere_t(float at, const Ray& r, V3 center, floa
     return !(det < 0.0f) && !(t < 0.0f) && t < at;
 }
 
+// The same test with the shader's early returns, for the full-warp phase: there the issue slots are the budget, and a
+// warp whose lanes all miss a sphere (the sky, the floor) skips its square root and the rest
+__device__ __forceinline__ bool sphere_tb(float at, const Ray& r, V3 center, float& t) {
+    const V3 op = center - r.origin;
+    const float b = dot(op, r.direction);
+    const float det = b * b - dot(op, op) + 1.0f * 1.0f;
+    if (det < 0.0f) return false;
+    const float sq = sqrtf(det);
+    t = b - sq;
+    if (t < 0.0f) t = b + sq;
+    return !(t < 0.0f) && t < at;
+}
+
 // the winner's normal and material (rt.wgsl:91-94): centres differ only in x (-2, 0, 2 = 2 * which - 4), radius 1;
 // which: 0 plane, 1..3 spheres, < 0 no hit
 __device__ __forceinline__ Hit surface(int which, float t, const Ray& ray) {
@@ -172,9 +185,9 @@ __device__ __forceinline__ Hit intersect_scene(const Ray& ray) {
     float best = 1e10f, t;
     int which = -1;
     if (plane_t(best, ray, t)) { best = t; which = 0; }
-    if (sphere_t(best, ray, v3(-2.0f, 1.0f, 0.0f), t)) { best = t; which = 1; }
-    if (sphere_t(best, ray, v3(0.0f, 1.0f, 0.0f), t)) { best = t; which = 2; }
-    if (sphere_t(best, ray, v3(2.0f, 1.0f, 0.0f), t)) { best = t; which = 3; }
+    if (sphere_tb(best, ray, v3(-2.0f, 1.0f, 0.0f), t)) { best = t; which = 1; }
+    if (sphere_tb(best, ray, v3(0.0f, 1.0f, 0.0f), t)) { best = t; which = 2; }
+    if (sphere_tb(best, ray, v3(2.0f, 1.0f, 0.0f), t)) { best = t; which = 3; }
     return surface(which, best, ray);
 }
 
@@ -183,9 +196,9 @@ __device__ __forceinline__ Hit intersect_scene(const Ray& ray) {
 __device__ __forceinline__ bool occluded(const Ray& r) {
     float t;
     bool any = plane_t(1e10f, r, t);
-    any |= sphere_t(1e10f, r, v3(-2.0f, 1.0f, 0.0f), t);
-    any |= sphere_t(1e10f, r, v3(0.0f, 1.0f, 0.0f), t);
-    any |= sphere_t(1e10f, r, v3(2.0f, 1.0f, 0.0f), t);
+    any |= sphere_tb(1e10f, r, v3(-2.0f, 1.0f, 0.0f), t);
+    any |= sphere_tb(1e10f, r, v3(0.0f, 1.0f, 0.0f), t);
+    any |= sphere_tb(1e10f, r, v3(2.0f, 1.0f, 0.0f), t);
     return any;
 }
 
