@@ -429,7 +429,11 @@ __device__ __forceinline__ void walk_begin(const SceneView& S, float3 o, float3 
 // Walk stack: (child, entry distance) pairs.  The first kSmemStack levels of every thread live in
 // shared memory (level-major, one 8-byte word per thread: conflict-free), deeper levels in local
 // memory - so the hot part of the stacks no longer competes with the tree for L1.
-constexpr int kSmemStack = 16, kStackCap = 64, kWalkBlock = 128;
+// 8 levels in shared memory (8 KB per CTA): 16 cost L1 capacity for no gain, 24 lost 8 % (profiles/r04i_occ.txt, r04w)
+#ifndef FORMA_SMEM_STACK
+#define FORMA_SMEM_STACK 8
+#endif
+constexpr int kSmemStack = FORMA_SMEM_STACK, kStackCap = 64, kWalkBlock = 128;
 struct WalkStack {
     int2* smem;   // this thread's column: level l at smem[l * kWalkBlock]
     int2* local;  // levels >= kSmemStack
