@@ -208,9 +208,12 @@ int upload_scene(forma_rt* c) {
         const int NS = (int)ns, NT = (int)nt, N = NS + NT;
         std::vector<V3> lo(N), hi(N);
         for (int i = 0; i < NS; ++i) {
+            // Sphere::hit (sphere.rs:23-51) only uses radius * radius, so a negative radius (the hollow-sphere idiom, a
+            // negative scale.x in JSON) is legal and hits like |r|: boxes, pads and the cull use |r|
             const float4 sp = spheres[i];
-            lo[i] = {sp.x - sp.w, sp.y - sp.w, sp.z - sp.w};
-            hi[i] = {sp.x + sp.w, sp.y + sp.w, sp.z + sp.w};
+            const float ar = std::fabs(sp.w);
+            lo[i] = {sp.x - ar, sp.y - ar, sp.z - ar};
+            hi[i] = {sp.x + ar, sp.y + ar, sp.z + ar};
         }
         for (int t = 0; t < NT; ++t) {
             const float4 a = tris[3 * t], e1 = tris[3 * t + 1], e2 = tris[3 * t + 2];
@@ -244,6 +247,8 @@ int upload_scene(forma_rt* c) {
             for (int k = 0; k < nbig; ++k) big[order[k]] = 1;
         }
         for (int i = 0; i < N; ++i) if (!std::isfinite(extent(i))) big[i] = 1;  // NaN/inf geometry stays on the exact scan
+        // so does a sphere whose 1 / |r| is not finite (r = 0 or denormal): the sphere pad scales with max 1 / |r|
+        for (int i = 0; i < NS; ++i) if (!std::isfinite(1.0f / std::fabs(spheres[i].w))) big[i] = 1;
         // stable partition of the packed arrays: big first
         auto partition = [&](int first, int count, int stride, std::vector<float4>& data, std::vector<int>& objs_idx) {
             std::vector<float4> d2; std::vector<int> o2; d2.reserve(data.size()); o2.reserve(objs_idx.size());
@@ -296,8 +301,8 @@ int upload_scene(forma_rt* c) {
                 bin.qmin[k] = ul[k] - qstep[k];
                 bin.qinv[k] = 1.0f / qstep[k];
             }
-            bq = 0.0f;  // max 1/r over the spheres of the tree (the outsized ones were moved to the front)
-            for (int i = big_s; i < NS; ++i) bq = std::max(bq, 1.0f / spheres[i].w);
+            bq = 0.0f;  // max 1/|r| over the spheres of the tree (the outsized ones were moved to the front)
+            for (int i = big_s; i < NS; ++i) bq = std::max(bq, 1.0f / std::fabs(spheres[i].w));
             use_bvh = true;
         }
     }

@@ -178,6 +178,14 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
     write_out(P, col, x, y, lx, ly, live, tile_rgb);
 }
 
+// A batch is what a warp holds when the queue runs dry, i.e. the drain at the end of a launch: at 8 samples (256
+// paths, ~4 ms of a warp's time on config D) the tail cost 4-5 ms per launch - nothing on a 230 ms launch, 15 % of the
+// 30 ms launch each GPU of an 8-way tile split runs (tools/partition_probe.py: 36.3 -> 32.2 ms at 2 samples).
+#ifndef FORMA_BATCH_SAMPLES
+#define FORMA_BATCH_SAMPLES 2
+#endif
+constexpr int kBatchSamples = FORMA_BATCH_SAMPLES;
+
 // Tree-mode path tracer (persistent warps).  Two things make a pixel-per-thread loop slow on scenes
 // with real bounces: rays of one warp need very different numbers of LBVH nodes, and pixels of one
 // tile need very different numbers of rays (sky next to a cluster of spheres).  So here
@@ -196,62 +204,90 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
 //      kWalk     resumable LBVH walk
 //    The warp walks until `refill` lanes have finished their walk (or none is walking), then those
 //    lanes shade, scatter or draw their next job and rejoin.
-enum : int { kNewPath = 0, kStart = 1, kWalk = 2, kShade = 3 };
-// A batch is what a warp holds when the queue runs dry, i.e. the drain at the end of a launch: at 8 samples (256
-// paths, ~4 ms of a warp's time on config D) the tail cost 4-5 ms per launch - nothing on a 230 ms launch, 15 % of the
-// 30 ms launch each GPU of an 8-way tile split runs (tools/partition_probe.py: 36.3 -> 32.2 ms at 2 samples).
-#ifndef FORMA_BATCH_SAMPLES
-#define FORMA_BATCH_SAMPLES 2
-#endif
-constexpr int kBatchSamples = FORMA_BATCH_SAMPLES;
-
+//@@QUEUE@@
+enum : int { kNewPath = 0, kStart = 1, kWalk = 2, kShade = 3, kLaneDone = 4 };
 #ifndef FORMA_TREE_MIN_BLOCKS
 #define FORMA_TREE_MIN_BLOCKS 8  // 64 registers: 32 resident warps / SM (profiles/r01p_occ.txt: A 134 -> 122 ms, D 142 -> 138 ms)
 #endif
+#ifndef FORMA_STEPS_PER_VOTE
+#define FORMA_STEPS_PER_VOTE 2   // node steps between two looks at the warp's state (one ballot each): A 52.5 -> 51.0 ms, D 100.3 -> 97.8 ms
+#endif
+// What a lane keeps IN REGISTERS across the walk is deliberately small - the ray's grid (9), closest_so_far, the
+// winner (one unified primitive index), node, sp, the stack base and the phase.  Everything the node loop does not
+// read - the ray itself (o, d, a), the job (pixel, sample) and the depth - waits in a per-thread record in shared
+// memory (`cold`, 40 B per thread, conflict-free) and is loaded where a leaf is tested or a lane is shaded; the
+// HitRecord is rebuilt when the walk is over; the warp's batch lives in shared memory; the ray counter is
+// warp-uniform; the grid is parked in local memory between two entries of the walk loop so that the shading code
+// in between cannot make the allocator spill it.  Round 1's kernel carried ~20 more live values through the loop
+// and paid 6 LDL of spilled grid constants + ~16 address instructions per node visit at the 64-register cap
+// (profiles/r04i_occ.txt r04q, r05a_A): 13.5 -> 17.6 lanes per instruction, 344 -> 301 warp instructions per ray.
 // COUNT = true is the instrumented instantiation (forma_rt_walk_stats): the same traversal, plus two per-lane
 // counters - internal nodes visited and leaf primitives tested - summed into P.walk_counters.  Never timed.
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_kernel(const __grid_constant__ RenderParams P) {
     const SceneView& S = P.scene;
     const float4 *sph = S.spheres, *tri = S.tris;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr unsigned kFull = 0xffffffffu;
     // this launch owns the 32x4 tiles t = j * part_mod + part_rem of a part_pitch-wide tile grid (the scan kernel's
     // CTA tiles; columns >= ctas_x are padding); each is four 8x4 warp tiles
-    const uint32_t ctas_x = (P.width + kTileW - 1) / kTileW, ctas = P.part_pitch * ((P.height + kTileH - 1) / kTileH);
+    const uint32_t ctas = P.part_pitch * ((P.height + kTileH - 1) / kTileH);
     const uint32_t own = ctas > P.part_rem ? (ctas - P.part_rem + P.part_mod - 1) / P.part_mod : 0u;
     const uint32_t groups = (P.chunk_k + kBatchSamples - 1) / kBatchSamples;
     const uint32_t n_batches = own * 4u * groups;  // < 2^32: checked by the launcher
-    uint32_t batch_next = 0, batch_jobs = 0, batch_x = 0, batch_y = 0, batch_k0 = 0;  // warp-uniform
-    const float fw = (float)P.width, fh = (float)P.height;
-    const bool no_jitter = P.flags & FORMA_RT_NO_JITTER, pinhole = P.flags & FORMA_RT_PINHOLE;
+    const uint32_t npix = P.width * P.height;
+    // the warp's current batch (warp-uniform, touched only when lanes are refilled): next job, jobs, x, y, first sample
+    __shared__ uint32_t batch_smem[kBlock / 32][8];
+    volatile uint32_t* batch = batch_smem[warp];
+    if (lane < 8) batch[lane] = 0u;
+    __syncwarp();
+    // the lane's cold state: [0] = (o, a), [1] = (d, depth), job = (pixel, sample)
+    __shared__ float4 cold_smem[2][kBlock];
+    __shared__ uint2 job_smem[kBlock];
+    auto cold_o = [&](float3& o, float& a) { const float4 v = cold_smem[0][threadIdx.x]; o = xyz(v); a = v.w; };
+    auto cold_d = [&](float3& d, uint32_t& depth) { const float4 v = cold_smem[1][threadIdx.x]; d = xyz(v); depth = __float_as_uint(v.w); };
 
-    uint32_t rays = 0;
+    uint32_t rays = 0;          // warp-uniform: every lane counts the warp's closest-hit queries
     unsigned long long n_nodes = 0, n_leaves = 0;  // COUNT only
     int astack[kMaxDepthCap];   // list indices of the hit objects: attenuations multiply innermost first
     __shared__ int2 stack_smem[kSmemStack * kWalkBlock];
-    int2 stack_local[kStackCap - kSmemStack];
-    const WalkStack wstack{stack_smem + threadIdx.x, stack_local};
-    PathRng rng{P.rk, 0u, 0u};
-    uint32_t depth = 0, slot = 0;  // slot: where this path's radiance goes in `rad`
+    int2 stack_local[kStackCap];
     int phase = kNewPath;
-    bool lane_done = false;
-    float3 o = f3(0.0f, 0.0f, 0.0f), d = o;
-    float a = 0.0f;
-    HitState h;
-    Winner w;
-    Walk W;
-    h.t = 0.0f; h.p = o; h.n = o; h.closest = FLT_MAX; h.obj = -1;
-    W.g = RayGrid{}; W.node = kWalkDone; W.sp = 0;
+    float closest = FLT_MAX;
+    int winner = -1;            // unified primitive index of the nearest accepted hit of the tree's run
+    float grid_park[9];
+    volatile float* gpark = grid_park;
+    auto park = [&](const RayGrid& g) {
+        gpark[0] = g.ax; gpark[1] = g.ay; gpark[2] = g.az; gpark[3] = g.blx; gpark[4] = g.bly; gpark[5] = g.blz;
+        gpark[6] = g.bhx; gpark[7] = g.bhy; gpark[8] = g.bhz;
+    };
+    int node = kWalkDone, sp = 0;
+
+    // planes that precede the tree's run in Scene.objects (tracer.rs:195-200 meets them first)
+    auto planes_before_tree = [&](float3 o, float3 d, HitState& h) {
+        h.t = 0.0f; h.p = f3(0.0f, 0.0f, 0.0f); h.n = h.p;
+        h.closest = FLT_MAX; h.obj = -1;
+        for (int sg = 0; sg < S.tree_seg; ++sg) {
+            const Segment sgm = S.segments[sg];
+            if (sgm.plane >= 0) plane_hit(S, sgm.plane, o, d, h);
+        }
+    };
 
     for (;;) {
         // ---- A. shade the rays whose walk has finished
         if (phase == kShade) {
+            float3 o, d; float a; uint32_t depth;
+            cold_o(o, a); cold_d(d, depth);
+            const uint2 job = job_smem[threadIdx.x];
+            const PathRng rng{P.rk, job.x, job.y};
+            HitState h;
+            planes_before_tree(o, d, h);   // the HitRecord as the scan left it in front of the run (not kept across the walk)
+            h.closest = closest;
             for (int sg = S.tree_seg; sg < S.n_segments; ++sg) {
-                Segment g = S.seg0;
-                if (sg > 0) g = S.segments[sg];
-                if (sg == S.tree_seg) finalize_winner(sph, tri, o, d, w, h);
-                if (g.plane >= 0) plane_hit(S, g.plane, o, d, h);
+                Segment sgm = S.seg0;
+                if (sg > 0) sgm = S.segments[sg];
+                if (sg == S.tree_seg) finalize_winner(sph, tri, o, d, winner_of(S, winner), h);
+                if (sgm.plane >= 0) plane_hit(S, sgm.plane, o, d, h);
             }
             float3 pc = f3(0.0f, 0.0f, 0.0f);
             bool done = true;
@@ -261,7 +297,8 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
                 if (scatter(S, rng, 1u + depth, d, h, no, nd)) {
                     astack[depth] = h.obj;
                     ++depth;
-                    o = no; d = nd;
+                    cold_smem[0][threadIdx.x] = make_float4(no.x, no.y, no.z, dot(nd, nd));  // a: sphere.rs:25
+                    cold_smem[1][threadIdx.x] = make_float4(nd.x, nd.y, nd.z, __uint_as_float(depth));
                     done = false;
                 }
             }
@@ -272,7 +309,9 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
                     --depth;
                     pc = attenuation(S, astack[depth]) * pc;
                 }
-                P.rad[slot] = make_float4(pc.x, pc.y, pc.z, 1.0f);
+                // where this path's radiance goes in `rad`: [sample in chunk][pixel]
+                const uint32_t k = rng.sample - P.sample_offset - P.chunk_base;
+                P.rad[(size_t)k * npix + rng.pixel] = make_float4(pc.x, pc.y, pc.z, 1.0f);
                 phase = kNewPath;
             }
         }
@@ -280,103 +319,110 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
         // kBatchSamples consecutive samples of one 8x4 tile, job j = (sample j >> 5, pixel j & 31), so
         // a refilled lane stays inside the tile its neighbours are tracing; one atomic per batch.
         for (;;) {
-            const bool want = phase == kNewPath && !lane_done;
+            const bool want = phase == kNewPath;
             const unsigned need = __ballot_sync(kFull, want);
             if (need == 0u) break;
+            uint32_t batch_next = batch[0], batch_jobs = batch[1];
             if (batch_next >= batch_jobs) {  // warp-uniform: draw the next batch
-                unsigned b = 0;
-                if (lane == 0) b = atomicAdd(P.job_counter, 1u);
-                b = __shfl_sync(kFull, b, 0);
-                if (b >= n_batches) { if (want) lane_done = true; break; }
-                const uint32_t sub = b / groups, grp = b % groups, t = (sub >> 2) * P.part_mod + P.part_rem;
-                batch_x = (t % P.part_pitch) * kTileW + (sub & 3u) * 8u; batch_y = (t / P.part_pitch) * kTileH;
-                batch_k0 = grp * kBatchSamples;
-                batch_jobs = batch_x < P.width ? min((uint32_t)kBatchSamples, P.chunk_k - batch_k0) * 32u : 0u;  // padding column
+                unsigned bi = 0;
+                if (lane == 0) bi = atomicAdd(P.job_counter, 1u);
+                bi = __shfl_sync(kFull, bi, 0);
+                if (bi >= n_batches) { if (want) phase = kLaneDone; break; }
+                const uint32_t sub = bi / groups, grp = bi % groups, t = (sub >> 2) * P.part_mod + P.part_rem;
+                const uint32_t bx = (t % P.part_pitch) * kTileW + (sub & 3u) * 8u, by = (t / P.part_pitch) * kTileH;
+                const uint32_t k0 = grp * kBatchSamples;
+                batch_jobs = bx < P.width ? min((uint32_t)kBatchSamples, P.chunk_k - k0) * 32u : 0u;  // padding column
                 batch_next = 0;
+                __syncwarp();
+                if (lane == 0) { batch[0] = 0u; batch[1] = batch_jobs; batch[2] = bx; batch[3] = by; batch[4] = k0; }
+                __syncwarp();
                 if (batch_jobs == 0u) continue;
             }
             const uint32_t job = batch_next + __popc(need & ((1u << lane) - 1u));
-            batch_next = min(batch_next + (uint32_t)__popc(need), batch_jobs);
+            const uint32_t bx = batch[2], by = batch[3], k0 = batch[4];
+            __syncwarp();
+            if (lane == 0) batch[0] = min(batch_next + (uint32_t)__popc(need), batch_jobs);
+            __syncwarp();
             if (want && job < batch_jobs) {
                 // ---- C. decode the job, generate its camera ray
-                const uint32_t jx = batch_x + (job & 7u), jy = batch_y + ((job >> 3) & 3u), k = batch_k0 + (job >> 5);
+                const uint32_t jx = bx + (job & 7u), jy = by + ((job >> 3) & 3u), k = k0 + (job >> 5);
                 if (jx < P.width && jy < P.height) {  // jobs of pixels outside the image (edge tiles) are dropped
-                    rng.pixel = jx + jy * P.width;
-                    rng.sample = P.sample_offset + P.chunk_base + k;
-                    slot = k * (P.width * P.height) + rng.pixel;
+                    const float fw = (float)P.width, fh = (float)P.height;
+                    const PathRng rng{P.rk, jx + jy * P.width, P.sample_offset + P.chunk_base + k};
                     Rand4 r0 = rng.block(0, 0);
-                    if (no_jitter) { r0.x = 0.5f; r0.y = 0.5f; }
+                    if (P.flags & FORMA_RT_NO_JITTER) { r0.x = 0.5f; r0.y = 0.5f; }
                     const float u = div_const((float)jx + r0.x, fw, P.inv_w, P.fast_div != 0u);                // tracer.rs:171
                     const float v = div_const((float)(P.height - jy) + r0.y, fh, P.inv_h, P.fast_div != 0u);   // tracer.rs:172 (Q1: height - y)
-                    camera_ray(P.cam, rng, r0, u, v, pinhole, o, d);
-                    depth = 0;
+                    float3 o, d;
+                    camera_ray(P.cam, rng, r0, u, v, (P.flags & FORMA_RT_PINHOLE) != 0u, o, d);
+                    cold_smem[0][threadIdx.x] = make_float4(o.x, o.y, o.z, dot(d, d));  // a: sphere.rs:25
+                    cold_smem[1][threadIdx.x] = make_float4(d.x, d.y, d.z, __uint_as_float(0u));
+                    job_smem[threadIdx.x] = make_uint2(rng.pixel, rng.sample);
                     phase = kStart;
                 }
             }
         }
         // ---- D. tracer.rs:190-194, then everything the scan meets before the tree
+        rays += __popc(__ballot_sync(kFull, phase == kStart));
         if (phase == kStart) {
-            ++rays;
-            h.t = 0.0f; h.p = f3(0.0f, 0.0f, 0.0f); h.n = h.p;
-            h.closest = FLT_MAX; h.obj = -1;
-            w = Winner{};
-            a = dot(d, d);  // sphere.rs:25
-            for (int sg = 0; sg < S.tree_seg; ++sg) {  // plane-only segments in front of the run
-                const Segment g = S.segments[sg];
-                if (g.plane >= 0) plane_hit(S, g.plane, o, d, h);
-            }
+            float3 o, d; float a; uint32_t depth;
+            cold_o(o, a); cold_d(d, depth);
+            closest = FLT_MAX;
+            if (S.tree_seg > 0) { HitState h; planes_before_tree(o, d, h); closest = h.closest; }
+            winner = -1;
             phase = kShade;
+            node = kWalkDone;
             if (!scene_culled(S, o, d, a)) {
-                for (int i = 0; i < S.big_spheres; ++i) try_sphere(S, sph, i, o, d, a, h, w);
-                for (int i = 0; i < S.big_tris; ++i) try_triangle(S, tri, i, o, d, h, w);
-                walk_begin(S, o, d, W);
+                for (int i = 0; i < S.big_spheres; ++i) try_prim(S, sph, tri, i, o, d, a, closest, winner);
+                for (int i = 0; i < S.big_tris; ++i) try_prim(S, sph, tri, S.n_spheres + i, o, d, a, closest, winner);
+                park(ray_grid(S, o, d));
+                node = 0; sp = 0;
                 phase = kWalk;
             }
         }
-        if (__ballot_sync(kFull, !lane_done) == 0u) break;  // the queue is empty and every lane has finished
+        if (__ballot_sync(kFull, phase != kLaneDone) == 0u) break;  // the queue is empty and every lane has finished
         // ---- E. walk until enough lanes are idle to be worth refilling
         {
-            // Convergent walk: per iteration every walking lane takes ONE stack entry (if it needs one)
-            // and tests ONE internal node, so lanes never wait for each other inside a node or a pop
-            // loop.  Lanes that reach a leaf, finish or idle stop progressing; the warp looks at them only
-            // once `leaf_batch` more lanes have stopped (one ballot per iteration until then), tests the
-            // waiting leaves together, and leaves the loop when `refill` lanes are ready to shade.
-            // Any visiting order gives the scan's result (Winner's tie rule).
+            // Convergent walk: per step every walking lane takes ONE stack entry (if it needs one) and tests ONE
+            // internal node, so lanes never wait for each other inside a node or a pop loop.  Lanes that reach a
+            // leaf, finish or idle stop progressing; the warp looks at them only once `leaf_batch` more lanes have
+            // stopped (one ballot per FORMA_STEPS_PER_VOTE steps until then), tests the waiting leaves together,
+            // and leaves the loop when `refill` lanes are ready to shade.  Any visiting order gives the scan's
+            // result (the tie rule of try_prim).  Lanes that are not walking hold node == kWalkDone, so the loop
+            // looks at `node` only.
             int wake_at = 0;
+            WalkStack wstack;
+            wstack.init(stack_smem + threadIdx.x, stack_local);
+            const RayGrid g{gpark[0], gpark[1], gpark[2], gpark[3], gpark[4], gpark[5], gpark[6], gpark[7], gpark[8]};
             for (;;) {
-                const bool walking = phase == kWalk;
-                if (walking && W.node == kWalkPop) {
-                    if (W.sp == 0) W.node = kWalkDone;
-                    else {
-                        const int2 e = wstack.at(--W.sp);
-                        if (__int_as_float(e.y) <= h.closest) W.node = e.x;  // else: stays kWalkPop
-                    }
+#pragma unroll
+                for (int step = 0; step < FORMA_STEPS_PER_VOTE; ++step) {
+                    walk_pop(node, sp, wstack, closest);
+                    if (COUNT && node >= 0) ++n_nodes;
+                    if (node >= 0) walk_inner(S, g, node, sp, wstack, closest);
                 }
-                if (COUNT && walking && W.node >= 0) ++n_nodes;
-                if (walking && W.node >= 0) walk_inner(S, W, wstack, h.closest);
-                const bool busy = walking && (W.node >= 0 || W.node == kWalkPop);
+                const bool busy = node >= 0 || node == kWalkPop;
                 const int stopped = 32 - __popc(__ballot_sync(kFull, busy));
                 if (stopped < wake_at) continue;
-                if (walking && W.node == kWalkDone) phase = kShade;
+                if (phase == kWalk && node == kWalkDone) phase = kShade;
                 const bool at_leaf = phase == kWalk && !busy;
                 const unsigned leaves = __ballot_sync(kFull, at_leaf);
-                const int idle = __popc(__ballot_sync(kFull, !lane_done && phase != kWalk));
+                const int idle = __popc(__ballot_sync(kFull, phase != kLaneDone && phase != kWalk));
                 if (idle >= (int)P.refill || (stopped == 32 && leaves == 0u)) break;
                 if (at_leaf) {
                     if (COUNT) ++n_leaves;
-                    const int p = ~W.node;
-                    if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w);
-                    else try_triangle(S, tri, p - S.n_spheres, o, d, h, w);
-                    W.node = kWalkPop;
+                    float3 o, d; float a; uint32_t depth;
+                    cold_o(o, a); cold_d(d, depth);
+                    try_prim(S, sph, tri, ~node, o, d, a, closest, winner);
+                    node = kWalkPop;
                 }
                 wake_at = min(32, stopped - __popc(leaves) + (int)P.leaf_batch);
             }
         }
     }
 
-    // closest-hit query count: one atomic per warp
-    uint32_t wr = __reduce_add_sync(kFull, rays);
-    if (lane == 0 && wr) atomicAdd(P.rays, (unsigned long long)wr);
+    // closest-hit query count (warp-uniform)
+    if (lane == 0 && rays) atomicAdd(P.rays, (unsigned long long)rays);
     if (COUNT) {
         for (int m = 16; m >= 1; m >>= 1) {
             n_nodes += __shfl_xor_sync(kFull, n_nodes, m);

@@ -42,9 +42,10 @@ __global__ void leaf_kernel(LbvhInput in, float4* __restrict__ leaf_lo, float4* 
     if (i < in.n_bvh_spheres) {
         const int s = in.big_spheres + i;
         const float4 sp = in.spheres[s];
-        lo = make_float3(sp.x - sp.w, sp.y - sp.w, sp.z - sp.w);
-        hi = make_float3(sp.x + sp.w, sp.y + sp.w, sp.z + sp.w);
-        q = 1.0f / sp.w;
+        const float ar = fabsf(sp.w);  // sphere.rs:27 squares the radius: r and -r are the same sphere
+        lo = make_float3(sp.x - ar, sp.y - ar, sp.z - ar);
+        hi = make_float3(sp.x + ar, sp.y + ar, sp.z + ar);
+        q = 1.0f / ar;
         prim = s;
     } else {
         const int t = in.big_tris + (i - in.n_bvh_spheres);

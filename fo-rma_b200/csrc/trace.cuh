@@ -171,29 +171,34 @@ struct Winner {
 
 // Sphere::hit (sphere.rs:23-51).  The candidate root does not depend on t_max: root_one if it
 // exceeds t_min, else root_two; if root_one >= t_max then root_two >= root_one fails too.
-__device__ __forceinline__ void try_sphere(const SceneView& S, const float4* __restrict__ sph, int i, float3 o,
-                                           float3 d, float a, HitState& h, Winner& w) {
-    const float4 s = sph[i];
+// Returns the candidate (the caller checks t_min < root <= closest), or -1 when disc <= 0.
+__device__ __forceinline__ float sphere_root(const float4 s, float3 o, float3 d, float a) {
     const float3 oc = o - xyz(s);
     const float b = dot(oc, d);
     const float c = dot(oc, oc) - s.w * s.w;
     const float disc = b * b - a * c;
+    float root = -1.0f;
     if (disc > 0.0f) {
         const float sq = sqrtf(disc);
-        float root = (-b - sq) / a;
+        root = (-b - sq) / a;
         if (!(root > kTMin)) root = (-b + sq) / a;
-        if (root > kTMin && root <= h.closest) {
-            bool take = root < h.closest;
-            int obj = -1;
-            if (!take && w.kind >= 0) { obj = S.sphere_obj[i]; take = obj < w.obj; }
-            if (take) { h.closest = root; w.kind = 0; w.slot = i; w.obj = obj >= 0 ? obj : S.sphere_obj[i]; }
-        }
+    }
+    return root;
+}
+__device__ __forceinline__ void try_sphere(const SceneView& S, const float4* __restrict__ sph, int i, float3 o,
+                                           float3 d, float a, float& closest, Winner& w) {
+    const float root = sphere_root(sph[i], o, d, a);
+    if (root > kTMin && root <= closest) {
+        bool take = root < closest;
+        int obj = -1;
+        if (!take && w.kind >= 0) { obj = S.sphere_obj[i]; take = obj < w.obj; }
+        if (take) { closest = root; w.kind = 0; w.slot = i; w.obj = obj >= 0 ? obj : S.sphere_obj[i]; }
     }
 }
 
 // Triangle extension (DESIGN.md "Scene mapping"): division-free inside test, one division for t.
-__device__ __forceinline__ void try_triangle(const SceneView& S, const float4* __restrict__ tri, int i, float3 o,
-                                             float3 d, HitState& h, Winner& w) {
+// Returns t for a ray through the triangle (the caller checks t_min < t <= closest), else -1.
+__device__ __forceinline__ float triangle_t(const float4* __restrict__ tri, int i, float3 o, float3 d) {
     const float4 q0 = tri[3 * i], q1 = tri[3 * i + 1], q2 = tri[3 * i + 2];
     const float3 e1 = xyz(q1), e2 = xyz(q2);
     const float3 pvec = cross(d, e2);
@@ -201,21 +206,49 @@ __device__ __forceinline__ void try_triangle(const SceneView& S, const float4* _
     const float3 tvec = o - xyz(q0);
     const float uu = dot(tvec, pvec);
     const bool pos = det > 0.0f;
+    float t = -1.0f;
     // first half of the inside test before paying for qvec
     if (det != 0.0f && (pos ? uu >= 0.0f : uu <= 0.0f)) {
         const float3 qvec = cross(tvec, e1);
         const float vv = dot(d, qvec);
         const bool inside = pos ? (vv >= 0.0f && uu + vv <= det) : (vv <= 0.0f && uu + vv >= det);
-        if (inside) {
-            const float t = dot(e2, qvec) / det;
-            if (t > kTMin && t <= h.closest) {
-                bool take = t < h.closest;
-                int obj = -1;
-                if (!take && w.kind >= 0) { obj = S.tri_obj[i]; take = obj < w.obj; }
-                if (take) { h.closest = t; w.kind = 2; w.slot = i; w.obj = obj >= 0 ? obj : S.tri_obj[i]; }
-            }
-        }
+        if (inside) t = dot(e2, qvec) / det;
     }
+    return t;
+}
+__device__ __forceinline__ void try_triangle(const SceneView& S, const float4* __restrict__ tri, int i, float3 o,
+                                             float3 d, float& closest, Winner& w) {
+    const float t = triangle_t(tri, i, o, d);
+    if (t > kTMin && t <= closest) {
+        bool take = t < closest;
+        int obj = -1;
+        if (!take && w.kind >= 0) { obj = S.tri_obj[i]; take = obj < w.obj; }
+        if (take) { closest = t; w.kind = 2; w.slot = i; w.obj = obj >= 0 ? obj : S.tri_obj[i]; }
+    }
+}
+
+// The same acceptance rule on a UNIFIED primitive index p (< n_spheres: sphere p, else triangle p - n_spheres),
+// with the winner kept as one such index (-1 = none): what render_tree_kernel carries through its walk.  The
+// list index (Scene.objects position) is only looked up on a tie in t.
+__device__ __forceinline__ int prim_obj(const SceneView& S, int p) {
+    return p < S.n_spheres ? S.sphere_obj[p] : S.tri_obj[p - S.n_spheres];
+}
+__device__ __forceinline__ void try_prim(const SceneView& S, const float4* __restrict__ sph, const float4* __restrict__ tri,
+                                         int p, float3 o, float3 d, float a, float& closest, int& winner) {
+    const float t = p < S.n_spheres ? sphere_root(sph[p], o, d, a) : triangle_t(tri, p - S.n_spheres, o, d);
+    if (t > kTMin && t <= closest) {
+        bool take = t < closest;
+        if (!take && winner >= 0) take = prim_obj(S, p) < prim_obj(S, winner);
+        if (take) { closest = t; winner = p; }
+    }
+}
+__device__ __forceinline__ Winner winner_of(const SceneView& S, int p) {
+    Winner w;
+    if (p >= 0) {
+        const bool is_sphere = p < S.n_spheres;
+        w.kind = is_sphere ? 0 : 2; w.slot = is_sphere ? p : p - S.n_spheres; w.obj = prim_obj(S, p);
+    }
+    return w;
 }
 
 // What the last accepting hit() of a segment left in the shared HitRecord (sphere.rs:33-36,42-45).
@@ -390,14 +423,14 @@ __device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __
         if (hitL && hitR) {
             if (nearR < nearL) { const int t = cL; cL = cR; cR = t; }  // cL = nearer child
             // leaves are tested on the spot, internal nodes are descended / pushed
-            if (cL < 0) { const int p = ~cL; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
+            if (cL < 0) { const int p = ~cL; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h.closest, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h.closest, w); }
             else { next = cL; have = true; }
-            if (cR < 0) { const int p = ~cR; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
+            if (cR < 0) { const int p = ~cR; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h.closest, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h.closest, w); }
             else if (have) { stack[sp++] = cR; }
             else { next = cR; have = true; }
         } else if (hitL || hitR) {
             const int c = hitL ? cL : cR;
-            if (c < 0) { const int p = ~c; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h, w); }
+            if (c < 0) { const int p = ~c; if (p < S.n_spheres) try_sphere(S, sph, p, o, d, a, h.closest, w); else try_triangle(S, tri, p - S.n_spheres, o, d, h.closest, w); }
             else { next = c; have = true; }
         }
         if (have) { node = next; continue; }
@@ -414,51 +447,71 @@ __device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __
 constexpr int kWalkDone = (int)0x80000000;  // never a leaf code: leaves are ~l with l < 2^31 - 2
 constexpr int kWalkPop = (int)0x80000001;   // convergent walk: this lane takes its next node from the stack
 
-struct Walk {
-    RayGrid g;
-    int node;  // >= 0 internal, < 0 leaf ~node, kWalkDone, kWalkPop
-    int sp;
-};
-
-__device__ __forceinline__ void walk_begin(const SceneView& S, float3 o, float3 d, Walk& W) {
-    W.g = ray_grid(S, o, d);
-    W.node = 0;
-    W.sp = 0;
-}
-
 // Walk stack: (child, entry distance) pairs.  The first kSmemStack levels of every thread live in
 // shared memory (level-major, one 8-byte word per thread: conflict-free), deeper levels in local
-// memory - so the hot part of the stacks no longer competes with the tree for L1.
+// memory - so the hot part of the stacks does not compete with the tree for L1.  The shared-window
+// address of the thread's column is computed ONCE and kept in a register (`sbase`, handed through an
+// opaque asm so the compiler cannot rematerialise it from S2R + shifts at every push and pop: that
+// cost 8 instructions per stack access in round 1's kernel, profiles/r05a_*).
 // 8 levels in shared memory (8 KB per CTA): 16 cost L1 capacity for no gain, 24 lost 8 % (profiles/r04i_occ.txt, r04w)
 #ifndef FORMA_SMEM_STACK
 #define FORMA_SMEM_STACK 8
 #endif
 constexpr int kSmemStack = FORMA_SMEM_STACK, kStackCap = 64, kWalkBlock = 128;
 struct WalkStack {
-    int2* smem;   // this thread's column: level l at smem[l * kWalkBlock]
-    int2* local;  // levels >= kSmemStack
-    __device__ __forceinline__ void push(int sp, int2 e) const {
-        if (sp < kSmemStack) smem[sp * kWalkBlock] = e;
-        else local[sp - kSmemStack] = e;
+    uint32_t sbase;  // shared-window byte address of level 0 of this thread; level l at sbase + l * 8 * kWalkBlock
+    int2* local;     // levels >= kSmemStack, indexed by the level itself (the first kSmemStack entries are never touched)
+    __device__ __forceinline__ void init(int2* smem_col, int2* local_levels) {
+        const uint32_t a = (uint32_t)__cvta_generic_to_shared(smem_col);
+        asm volatile("mov.u32 %0, %1;" : "=r"(sbase) : "r"(a));
+        local = local_levels;
     }
-    __device__ __forceinline__ int2 at(int sp) const { return sp < kSmemStack ? smem[sp * kWalkBlock] : local[sp - kSmemStack]; }
+    // entry `sp` <- (child, dist) when `on` (one predicated store; the local levels are a rarely taken branch)
+    __device__ __forceinline__ void push_if(bool on, int sp, int child, float dist) const {
+        const uint32_t addr = sbase + (uint32_t)sp * (8u * kWalkBlock);
+        asm volatile("{ .reg .pred p; setp.ne.b32 p, %3, 0; @p st.shared.v2.b32 [%0], {%1, %2}; }"
+                     ::"r"(addr), "r"(child), "r"(__float_as_int(dist)), "r"((int)(on && sp < kSmemStack)) : "memory");
+        if (on && sp >= kSmemStack) local[sp] = make_int2(child, __float_as_int(dist));
+    }
+    // (child, dist) <- entry `sp` when `on`, else both are left as they are
+    __device__ __forceinline__ void load_if(bool on, int sp, int& child, float& dist) const {
+        const uint32_t addr = sbase + (uint32_t)sp * (8u * kWalkBlock);
+        int c = child, f = __float_as_int(dist);
+        asm volatile("{ .reg .pred p; setp.ne.b32 p, %3, 0; @p ld.shared.v2.b32 {%0, %1}, [%2]; }"
+                     : "+r"(c), "+r"(f) : "r"(addr), "r"((int)(on && sp < kSmemStack)) : "memory");
+        if (on && sp >= kSmemStack) { const int2 e = local[sp]; c = e.x; f = e.y; }
+        child = c; dist = __int_as_float(f);
+    }
 };
+
+// A lane that needs a node takes ONE stack entry: the entry's child if its entry distance is still in range,
+// else it stays kWalkPop (and takes the next entry in the next iteration); an empty stack ends the walk.
+__device__ __forceinline__ void walk_pop(int& node, int& sp, const WalkStack& stack, float closest) {
+    const bool popping = node == kWalkPop;
+    const bool take = popping && sp > 0;
+    sp -= take ? 1 : 0;
+    int child = 0;
+    float dist = 0.0f;
+    stack.load_if(take, sp, child, dist);
+    const int next = take ? (dist <= closest ? child : kWalkPop) : kWalkDone;
+    node = popping ? next : node;
+}
 
 // One internal node: test both child boxes, descend into the nearer hit child (pushing the other), or ask
 // for the next stack entry (kWalkPop, taken by the caller's next iteration).
-__device__ __forceinline__ void walk_inner(const SceneView& S, Walk& W, const WalkStack& stack, float closest) {
-    const QNode n = load_node(S.bvh_nodes, W.node);
+__device__ __forceinline__ void walk_inner(const SceneView& S, const RayGrid& g, int& node, int& sp, const WalkStack& stack,
+                                           float closest) {
+    const QNode n = load_node(S.bvh_nodes, node);
     float nearL, farL, nearR, farR;
-    slab_pair(n, W.g, closest, nearL, farL, nearR, farR);
+    slab_pair(n, g, closest, nearL, farL, nearR, farR);
     const bool hitL = nearL <= farL, hitR = nearR <= farR;
-    const int cL = n.cL, cR = n.cR;
-    if (hitL && hitR) {
-        const bool swap = nearR < nearL;  // descend into the nearer child, push the other
-        W.node = swap ? cR : cL;
-        stack.push(W.sp++, make_int2(swap ? cL : cR, __float_as_int(swap ? nearL : nearR)));
-    } else if (hitL) W.node = cL;
-    else if (hitR) W.node = cR;
-    else W.node = kWalkPop;
+    const bool both = hitL && hitR;
+    const bool r_first = hitR && (!hitL || nearR < nearL);  // which child is entered when at least one is hit
+    const int enter = r_first ? n.cR : n.cL, other = r_first ? n.cL : n.cR;
+    // both hit: the other child waits on the stack with ITS entry distance, the larger of the two
+    stack.push_if(both, sp, other, fmaxf(nearL, nearR));
+    sp += both ? 1 : 0;
+    node = (hitL || hitR) ? enter : kWalkPop;
 }
 
 // MODE selects what a kernel instantiation carries: the brute-force scan with the primitives staged
@@ -485,8 +538,8 @@ __device__ __forceinline__ void closest_hit(const SceneView& S, const float4* __
             if (tree) { sph_end = S.big_spheres; tri_end = S.big_tris; }
         }
         if (!culled) {
-            for (int i = g.sph_begin; i < sph_end; ++i) try_sphere(S, sph, i, o, d, a, h, w);
-            for (int i = g.tri_begin; i < tri_end; ++i) try_triangle(S, tri, i, o, d, h, w);
+            for (int i = g.sph_begin; i < sph_end; ++i) try_sphere(S, sph, i, o, d, a, h.closest, w);
+            for (int i = g.tri_begin; i < tri_end; ++i) try_triangle(S, tri, i, o, d, h.closest, w);
             if constexpr (MODE == kTree) {
                 if (tree) bvh_closest(S, sph, tri, o, d, a, h, w);
             }
