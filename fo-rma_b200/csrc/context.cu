@@ -584,6 +584,38 @@ int forma_rt_camera_set(forma_rt* ctx, const forma_rt_camera* cam) {
 // ---- rendering ---------------------------------------------------------------------------------------
 namespace {
 
+// Scan mode has two kernels (kernels.cu): a pixel per thread (render_kernel: unbeatable while a frame is mostly sky -
+// config C runs its camera-ray -> sky loop - and for a 1-spp frame, where a queue has nothing to refill lanes with)
+// and (pixel, sample) jobs from a queue (render_queue_kernel: balanced whatever the per-pixel cost).  The queue is
+// used for multi-sample frames that can bounce: planes or non-finite geometry (the beam cull of render_kernel never
+// applies), or the scene's bounding sphere covers more than a fifth of a coarse grid of primary rays (f64, same
+// geometry as beam_culled: distance of the central ray to the sphere's centre).  FORMA_RT_SCAN_QUEUE=0 / 1 overrides
+// (A/B measurements).
+bool frame_bounces(const forma_rt* c, uint32_t spp) {
+    if (const char* e = std::getenv("FORMA_RT_SCAN_QUEUE")) return std::atoi(e) != 0;
+    if (spp < 4) return false;
+    const forma::SceneView& v = c->view;
+    if (v.n_spheres + v.n_tris + v.n_planes == 0) return false;
+    if (v.n_planes != 0 || !(v.cull_r2 < FLT_MAX)) return true;
+    const forma_rt_camera& k = c->scene.camera.c;
+    const double R = std::sqrt((double)v.cull_r2) * 1.05;
+    int hit = 0, n = 0;
+    for (int gy = 0; gy < 27; ++gy)
+        for (int gx = 0; gx < 48; ++gx, ++n) {
+            const double s = (gx + 0.5) / 48.0, t = (gy + 0.5) / 27.0;
+            double D[3], m[3], dd = 0.0, md = 0.0, mm = 0.0;
+            for (int i = 0; i < 3; ++i) {
+                D[i] = (double)k.lower_left_corner[i] + s * (double)k.horizontal[i] + t * (double)k.vertical[i] - (double)k.position[i];
+                m[i] = (double)k.position[i] - (double)v.cull_center[i];
+                dd += D[i] * D[i]; md += m[i] * D[i]; mm += m[i] * m[i];
+            }
+            // closest approach of pos + tau D, tau >= 0, to the centre
+            const double d2 = (md < 0.0 && dd > 0.0) ? mm - md * md / dd : mm;
+            hit += !(d2 > R * R);  // NaN counts as a hit
+        }
+    return hit * 5 > n;
+}
+
 // One launch of the trace kernel on `stream`; outputs are device pointers.  Records kernel events.
 int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t max_depth, uint32_t flags,
                      uint8_t* d_rgb, float4* d_sum, cudaStream_t stream, const float4* d_prior = nullptr,
@@ -604,7 +636,8 @@ int render_on_device(forma_rt* c, uint32_t spp, uint32_t sample_offset, uint32_t
     P.part_mod = c->part_mod; P.part_rem = c->part_rem;
     P.part_pitch = (c->width + 31) / 32;  // smallest pitch >= tiles per row that is coprime with part_mod
     while (std::gcd(P.part_pitch, P.part_mod) != 1u) ++P.part_pitch;
-    if (P.scene.bvh_nodes) {  // tree mode: rad holds a chunk of samples of the frame, <= kRadBudget bytes
+    P.queue = (!P.scene.bvh_nodes && frame_bounces(c, spp)) ? 1u : 0u;
+    if (P.scene.bvh_nodes || P.queue) {  // job-queue modes: rad holds a chunk of samples of the frame, <= kRadBudget bytes
         const size_t npix = (size_t)c->width * c->height;
         size_t chunk = kRadBudget / (npix * sizeof(float4));
         chunk = std::max<size_t>(1, std::min<size_t>({chunk, spp, 64}));

@@ -90,7 +90,8 @@ struct RenderParams {
     uint32_t part_mod, part_rem, part_pitch;
     float inv_w, inv_h;        // RN(1 / width), RN(1 / height)
     uint32_t fast_div;         // 1: div_const's multiply form was verified exhaustively for both divisors
-    // ---- tree mode only (render_tree_kernel + accumulate_kernel, kernels.cu) ----
+    uint32_t queue;            // scan mode: 1 = render_queue_kernel ((pixel, sample) jobs), 0 = render_kernel (a pixel per thread)
+    // ---- job-queue modes (render_tree_kernel / render_queue_kernel + accumulate_kernel, kernels.cu) ----
     float4* rad;               // [chunk sample][pixel] radiance of the finished paths of one chunk
     float4* acc;               // [pixel] running in-order sum across chunks
     unsigned int* job_counter; // next (pixel, sample) job of the chunk

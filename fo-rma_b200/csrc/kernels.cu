@@ -4,6 +4,7 @@
 //   tonemap_kernel       tracer.rs:177-184 on a summed f32 buffer
 //   reduce_tonemap_kernel  the cross-GPU exchange step fused with the write-out (peer loads)
 // Built with -fmad=false (see trace.cuh).
+#include <algorithm>
 #include <cstdio>
 
 #include "kernels.hpp"
@@ -42,8 +43,9 @@ __device__ __forceinline__ void write_out(const RenderParams& P, float3 col, uin
         // tracer.rs:177-184: average in linear space, sqrt gamma, (c * 255.0) as u8
         float3 c = col / n_spp;
         const uint32_t r = as_u8(sqrtf(c.x) * 255.0f), g = as_u8(sqrtf(c.y) * 255.0f), b = as_u8(sqrtf(c.z) * 255.0f);
+        // word stores need a 4-byte aligned frame (a caller's device pointer may be a slice) and rows that are whole words
         const bool full_tile = (blockIdx.x + 1) * kTileW <= P.width && (blockIdx.y + 1) * kTileH <= P.height &&
-                               (P.width * 3u) % 4u == 0;
+                               (P.width * 3u) % 4u == 0 && (reinterpret_cast<uintptr_t>(P.rgb) & 3u) == 0u;
         if (full_tile) {  // stage 4 rows x 96 bytes, write them as 96 coalesced 32-bit words
             tile_rgb[ly][lx * 3 + 0] = (uint8_t)r;
             tile_rgb[ly][lx * 3 + 1] = (uint8_t)g;
@@ -186,6 +188,110 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
 #endif
 constexpr int kBatchSamples = FORMA_BATCH_SAMPLES;
 
+// Scan-mode path tracer for frames that BOUNCE (the reference's own scenes, scenes.rs:6-156: a plane or a
+// radius-1000 ground sphere behind every pixel).  render_kernel above gives a pixel to a thread for all its samples:
+// on such frames a thread next to a silhouette traces 5-10x the rays of its neighbours, a 128-thread CTA runs as
+// long as its slowest pixel and the launch ends with a long tail (profiles/r05a_*: SMs busy 18 % of the elapsed
+// cycles at 600x600x50 spp, 55 % at 1080p x 64 spp).  Here the (pixel, sample) pairs are JOBS: persistent warps draw
+// them in batches (kBatchSamples samples of one 8x4 tile, one atomic per batch) and every lane takes its next job the
+// moment its path ends, so every lane of every warp traces one ray per iteration until the queue is empty.  A finished
+// path stores its radiance in rad[sample][pixel]; accumulate_kernel adds them per pixel in sample order (the f32
+// chain of tracer.rs:170-175: bit-identical sums).  600x600x50 spp: get_simple_scene 5.49 -> 1.17 ms, get_objects
+// 5.45 -> 1.31 ms.
+#ifndef FORMA_QUEUE_MIN_BLOCKS
+#define FORMA_QUEUE_MIN_BLOCKS 6
+#endif
+template <int MODE>
+__global__ void __launch_bounds__(kBlock, FORMA_QUEUE_MIN_BLOCKS) render_queue_kernel(const __grid_constant__ RenderParams P) {
+    const float4 *sph, *tri;
+    stage_scene<MODE>(P.scene, sph, tri);
+    const SceneView& S = P.scene;
+    const int lane = threadIdx.x & 31;
+    constexpr unsigned kFull = 0xffffffffu;
+    const uint32_t ctas = P.part_pitch * ((P.height + kTileH - 1) / kTileH);
+    const uint32_t own = ctas > P.part_rem ? (ctas - P.part_rem + P.part_mod - 1) / P.part_mod : 0u;
+    const uint32_t groups = (P.chunk_k + kBatchSamples - 1) / kBatchSamples;
+    const uint32_t n_batches = own * 4u * groups;
+    const uint32_t npix = P.width * P.height;
+    const float fw = (float)P.width, fh = (float)P.height;
+    const bool no_jitter = P.flags & FORMA_RT_NO_JITTER, pinhole = P.flags & FORMA_RT_PINHOLE;
+    uint32_t batch_next = 0, batch_jobs = 0, batch_x = 0, batch_y = 0, batch_k0 = 0;  // warp-uniform
+
+    uint32_t rays = 0;
+    int astack[kMaxDepthCap];  // list indices of the hit objects: attenuations multiply innermost first
+    PathRng rng{P.rk, 0u, 0u};
+    uint32_t depth = 0;
+    bool alive = false, lane_done = false;
+    float3 o = f3(0.0f, 0.0f, 0.0f), d = o;
+    for (;;) {
+        // ---- hand the warp's next jobs to the lanes whose path has ended (tracer.rs:171-173 for each)
+        for (;;) {
+            const bool want = !alive && !lane_done;
+            const unsigned need = __ballot_sync(kFull, want);
+            if (need == 0u) break;
+            if (batch_next >= batch_jobs) {  // warp-uniform: draw the next batch
+                unsigned bi = 0;
+                if (lane == 0) bi = atomicAdd(P.job_counter, 1u);
+                bi = __shfl_sync(kFull, bi, 0);
+                if (bi >= n_batches) { if (want) lane_done = true; break; }
+                const uint32_t sub = bi / groups, grp = bi % groups, t = (sub >> 2) * P.part_mod + P.part_rem;
+                batch_x = (t % P.part_pitch) * kTileW + (sub & 3u) * 8u; batch_y = (t / P.part_pitch) * kTileH;
+                batch_k0 = grp * kBatchSamples;
+                batch_jobs = batch_x < P.width ? min((uint32_t)kBatchSamples, P.chunk_k - batch_k0) * 32u : 0u;  // padding column
+                batch_next = 0;
+                if (batch_jobs == 0u) continue;
+            }
+            const uint32_t job = batch_next + __popc(need & ((1u << lane) - 1u));
+            batch_next = min(batch_next + (uint32_t)__popc(need), batch_jobs);
+            if (want && job < batch_jobs) {
+                const uint32_t jx = batch_x + (job & 7u), jy = batch_y + ((job >> 3) & 3u), k = batch_k0 + (job >> 5);
+                if (jx < P.width && jy < P.height) {  // jobs of pixels outside the image (edge tiles) are dropped
+                    rng.pixel = jx + jy * P.width;
+                    rng.sample = P.sample_offset + P.chunk_base + k;
+                    Rand4 r0 = rng.block(0, 0);
+                    if (no_jitter) { r0.x = 0.5f; r0.y = 0.5f; }
+                    const float u = div_const((float)jx + r0.x, fw, P.inv_w, P.fast_div != 0u);                // tracer.rs:171
+                    const float v = div_const((float)(P.height - jy) + r0.y, fh, P.inv_h, P.fast_div != 0u);   // tracer.rs:172 (Q1: height - y)
+                    camera_ray(P.cam, rng, r0, u, v, pinhole, o, d);
+                    depth = 0;
+                    alive = true;
+                }
+            }
+        }
+        if (__ballot_sync(kFull, alive) == 0u) break;  // the queue is empty and every path of the warp has ended
+        // ---- one closest-hit query per lane: get_color (tracer.rs:189-219), unrolled
+        if (alive) {
+            HitState h;
+            ++rays;
+            closest_hit<MODE>(S, sph, tri, o, d, h);
+            float3 pc = f3(0.0f, 0.0f, 0.0f);
+            bool done = true;
+            if (h.obj < 0) pc = sky(d);                      // tracer.rs:213-217
+            else if (depth < P.max_depth) {                  // tracer.rs:205
+                float3 no, nd;
+                if (scatter(S, rng, 1u + depth, d, h, no, nd)) {
+                    astack[depth] = h.obj;
+                    ++depth;
+                    o = no; d = nd;
+                    done = false;
+                }
+            }
+            if (done) {
+                if (black_path(S, pc)) depth = 0;
+                while (depth > 0) {  // tracer.rs:206-207 on the way back up
+                    --depth;
+                    pc = attenuation(S, astack[depth]) * pc;
+                }
+                const uint32_t k = rng.sample - P.sample_offset - P.chunk_base;
+                P.rad[(size_t)k * npix + rng.pixel] = make_float4(pc.x, pc.y, pc.z, 1.0f);
+                alive = false;
+            }
+        }
+    }
+    const uint32_t wr = __reduce_add_sync(kFull, rays);
+    if (lane == 0 && wr) atomicAdd(P.rays, (unsigned long long)wr);
+}
+
 // Tree-mode path tracer (persistent warps).  Two things make a pixel-per-thread loop slow on scenes
 // with real bounces: rays of one warp need very different numbers of LBVH nodes, and pixels of one
 // tile need very different numbers of rays (sky next to a cluster of spheres).  So here
@@ -204,7 +310,6 @@ constexpr int kBatchSamples = FORMA_BATCH_SAMPLES;
 //      kWalk     resumable LBVH walk
 //    The warp walks until `refill` lanes have finished their walk (or none is walking), then those
 //    lanes shade, scatter or draw their next job and rejoin.
-//@@QUEUE@@
 enum : int { kNewPath = 0, kStart = 1, kWalk = 2, kShade = 3, kLaneDone = 4 };
 #ifndef FORMA_TREE_MIN_BLOCKS
 #define FORMA_TREE_MIN_BLOCKS 8  // 64 registers: 32 resident warps / SM (profiles/r01p_occ.txt: A 134 -> 122 ms, D 142 -> 138 ms)
@@ -432,30 +537,67 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
     }
 }
 
-// tracer.rs:170-184 for tree mode: acc[p] += rad[0][p], rad[1][p], ... in sample order; after the last
-// chunk the f32 sum and / or the sqrt-gamma RGB8 pixel are written out.
+// Four RGB8 pixels = 12 bytes = three aligned 32-bit words: the write-out kernels below give a thread four
+// neighbouring pixels and store words, not bytes (the frame may be a peer GPU's, written over NVLink).
+__device__ __forceinline__ void store_rgb8x4(uint8_t* rgb, size_t first_pixel, const uint32_t r[4], const uint32_t g[4],
+                                             const uint32_t b[4]) {
+    uint32_t* w = reinterpret_cast<uint32_t*>(rgb + 3 * first_pixel);  // first_pixel % 4 == 0 and rgb 4-byte aligned
+    w[0] = r[0] | g[0] << 8 | b[0] << 16 | r[1] << 24;
+    w[1] = g[1] | b[1] << 8 | r[2] << 16 | g[2] << 24;
+    w[2] = b[2] | r[3] << 8 | g[3] << 16 | b[3] << 24;
+}
+// tracer.rs:177-184: average in linear space, sqrt gamma, (c * 255.0) as u8
+__device__ __forceinline__ void tone_rgb(float3 col, float n_spp, uint32_t& r, uint32_t& g, uint32_t& b) {
+    const float3 c = col / n_spp;
+    r = as_u8(sqrtf(c.x) * 255.0f); g = as_u8(sqrtf(c.y) * 255.0f); b = as_u8(sqrtf(c.z) * 255.0f);
+}
+
+// tracer.rs:170-184 for the job-queue modes: acc[p] += rad[0][p], rad[1][p], ... in sample order; after the last
+// chunk the f32 sum and / or the sqrt-gamma RGB8 pixel are written out.  A thread owns four neighbouring pixels
+// of a row (never more than one 32x4 tile, so the multi-GPU tile split keeps or skips them together).
 __global__ void accumulate_kernel(const __grid_constant__ RenderParams P, int first, int last) {
     const size_t npix = (size_t)P.width * P.height;
-    for (size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x; p < npix; p += (size_t)gridDim.x * blockDim.x) {
-        if (P.part_mod > 1u) {  // another GPU's tile: leave its pixels alone
-            const uint32_t x = (uint32_t)(p % P.width), y = (uint32_t)(p / P.width);
-            if (((y / kTileH) * P.part_pitch + x / kTileW) % P.part_mod != P.part_rem) continue;
+    const uint32_t gpr = (P.width + 3u) / 4u;  // groups per row
+    const size_t ngroups = (size_t)gpr * P.height;
+    const bool words = P.width % 4u == 0u && (reinterpret_cast<uintptr_t>(P.rgb) & 3u) == 0u;
+    for (size_t gi = blockIdx.x * (size_t)blockDim.x + threadIdx.x; gi < ngroups; gi += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t y = (uint32_t)(gi / gpr), x0 = (uint32_t)(gi % gpr) * 4u;
+        const uint32_t n = min(4u, P.width - x0);
+        if (P.part_mod > 1u && ((y / kTileH) * P.part_pitch + x0 / kTileW) % P.part_mod != P.part_rem) continue;  // another GPU's tile
+        const size_t p0 = (size_t)y * P.width + x0;
+        float3 col[4];
+#pragma unroll
+        for (uint32_t j = 0; j < 4u; ++j) {
+            col[j] = f3(0.0f, 0.0f, 0.0f);
+            if (j < n) {
+                if (!first) { const float4 c = P.acc[p0 + j]; col[j] = f3(c.x, c.y, c.z); }
+                else if (P.prior) col[j] = xyz(P.prior[p0 + j]);
+            }
         }
-        float3 col = f3(0.0f, 0.0f, 0.0f);
-        if (!first) { const float4 c = P.acc[p]; col = f3(c.x, c.y, c.z); }
-        else if (P.prior) col = xyz(P.prior[p]);
         for (uint32_t k = 0; k < P.chunk_k; ++k) {
-            const float4 r = P.rad[k * npix + p];
-            col = col + f3(r.x, r.y, r.z);  // tracer.rs:174
+            float4 r[4];
+#pragma unroll
+            for (uint32_t j = 0; j < 4u; ++j) r[j] = j < n ? P.rad[k * npix + p0 + j] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+            for (uint32_t j = 0; j < 4u; ++j) col[j] = col[j] + f3(r[j].x, r[j].y, r[j].z);  // tracer.rs:174
         }
-        if (!last) { P.acc[p] = make_float4(col.x, col.y, col.z, 0.0f); continue; }
+        if (!last) {
+#pragma unroll
+            for (uint32_t j = 0; j < 4u; ++j) if (j < n) P.acc[p0 + j] = make_float4(col[j].x, col[j].y, col[j].z, 0.0f);
+            continue;
+        }
         const float n_spp = (float)(P.spp + P.spp_prior);
-        if (P.sum) P.sum[p] = make_float4(col.x, col.y, col.z, n_spp);
+        if (P.sum) {
+#pragma unroll
+            for (uint32_t j = 0; j < 4u; ++j) if (j < n) P.sum[p0 + j] = make_float4(col[j].x, col[j].y, col[j].z, n_spp);
+        }
         if (P.rgb) {
-            const float3 c = col / n_spp;
-            P.rgb[3 * p + 0] = (uint8_t)as_u8(sqrtf(c.x) * 255.0f);
-            P.rgb[3 * p + 1] = (uint8_t)as_u8(sqrtf(c.y) * 255.0f);
-            P.rgb[3 * p + 2] = (uint8_t)as_u8(sqrtf(c.z) * 255.0f);
+            uint32_t r[4], g[4], b[4];
+#pragma unroll
+            for (uint32_t j = 0; j < 4u; ++j) tone_rgb(col[j], n_spp, r[j], g[j], b[j]);
+            if (words && n == 4u) store_rgb8x4(P.rgb, p0, r, g, b);
+            else
+                for (uint32_t j = 0; j < n; ++j) { uint8_t* px = P.rgb + 3 * (p0 + j); px[0] = (uint8_t)r[j]; px[1] = (uint8_t)g[j]; px[2] = (uint8_t)b[j]; }
         }
     }
 }
@@ -538,44 +680,75 @@ __global__ void __launch_bounds__(kBlock) primary_hits_kernel(const __grid_const
     P.t[i] = h.closest;
 }
 
-// tracer.rs:177-184 over pixels [begin, end) of a summed float4 buffer
+// tracer.rs:177-184 over pixels [begin, end) of a summed float4 buffer.  A thread owns the aligned group of four
+// pixels 4 g .. 4 g + 3: whole groups inside the range leave as three 32-bit words, the ragged ends as bytes.
 __global__ void tonemap_kernel(const float4* __restrict__ sum, float spp, uint64_t begin, uint64_t end,
                                uint8_t* __restrict__ rgb) {
-    for (uint64_t i = begin + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < end;
-         i += (uint64_t)gridDim.x * blockDim.x) {
-        const float4 s = sum[i];
-        float3 c = f3(s.x, s.y, s.z) / spp;
-        rgb[3 * i + 0] = (uint8_t)as_u8(sqrtf(c.x) * 255.0f);
-        rgb[3 * i + 1] = (uint8_t)as_u8(sqrtf(c.y) * 255.0f);
-        rgb[3 * i + 2] = (uint8_t)as_u8(sqrtf(c.z) * 255.0f);
+    const bool words = (reinterpret_cast<uintptr_t>(rgb) & 3u) == 0u;
+    const uint64_t g0 = begin / 4u, g1 = (end + 3u) / 4u;
+    for (uint64_t gi = g0 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; gi < g1; gi += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t p0 = 4u * gi;
+        uint32_t r[4], g[4], b[4];
+        bool in[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            in[j] = p0 + j >= begin && p0 + j < end;
+            const float4 s = in[j] ? sum[p0 + j] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            tone_rgb(f3(s.x, s.y, s.z), spp, r[j], g[j], b[j]);
+        }
+        if (words && in[0] && in[3]) store_rgb8x4(rgb, p0, r, g, b);
+        else
+            for (int j = 0; j < 4; ++j) if (in[j]) { uint8_t* px = rgb + 3 * (p0 + j); px[0] = (uint8_t)r[j]; px[1] = (uint8_t)g[j]; px[2] = (uint8_t)b[j]; }
     }
 }
 
 // Sample-split exchange fused with the write-out: each rank owns pixels [begin, end); it loads the
 // n_peers partial sums of those pixels straight from the peers' HBM over NVLink (P2P-mapped
-// pointers), adds them in rank order, and tone-maps — no intermediate reduced buffer in HBM.
+// pointers), adds them in rank order, and tone-maps — no intermediate reduced buffer in HBM.  Four pixels per
+// thread: 64 contiguous bytes from every peer in flight, and the RGB8 result - usually into rank 0's peer-mapped
+// frame - leaves as three 32-bit words instead of twelve single bytes.
 constexpr int kMaxPeers = 16;
 struct PeerPtrs {
     const float4* p[kMaxPeers];
 };
 __global__ void reduce_tonemap_kernel(const __grid_constant__ PeerPtrs peers, int n_peers, float spp, uint64_t begin,
                                       uint64_t end, uint8_t* __restrict__ rgb, float4* __restrict__ sum_out) {
-    for (uint64_t i = begin + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < end;
-         i += (uint64_t)gridDim.x * blockDim.x) {
-        float4 v[kMaxPeers];
+    const bool words = (reinterpret_cast<uintptr_t>(rgb) & 3u) == 0u;
+    const uint64_t g0 = begin / 4u, g1 = (end + 3u) / 4u;
+    for (uint64_t gi = g0 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; gi < g1; gi += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t p0 = 4u * gi;
+        bool in[4];
+        float4 acc[4];
 #pragma unroll
-        for (int r = 0; r < kMaxPeers; ++r)
-            if (r < n_peers) v[r] = __ldg(peers.p[r] + i);  // all peer loads in flight before the adds
-        float4 acc = v[0];
+        for (int j = 0; j < 4; ++j) { in[j] = p0 + j >= begin && p0 + j < end; acc[j] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); }
+        for (int r0 = 0; r0 < n_peers; r0 += 4) {  // 4 peers x 4 pixels = 16 loads in flight before the adds
+            float4 v[4][4];
 #pragma unroll
-        for (int r = 1; r < kMaxPeers; ++r)
-            if (r < n_peers) { acc.x += v[r].x; acc.y += v[r].y; acc.z += v[r].z; acc.w += v[r].w; }
-        if (sum_out) sum_out[i] = acc;
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    v[r][j] = (r0 + r < n_peers && in[j]) ? __ldg(peers.p[r0 + r] + p0 + j) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+                if (r0 + r < n_peers) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        if (r0 + r == 0) acc[j] = v[r][j];  // the sum STARTS with rank 0's partial (not 0 + it: -0 stays -0)
+                        else { acc[j].x += v[r][j].x; acc[j].y += v[r][j].y; acc[j].z += v[r][j].z; acc[j].w += v[r][j].w; }
+                    }
+                }
+        }
+        if (sum_out) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) if (in[j]) sum_out[p0 + j] = acc[j];
+        }
         if (rgb) {
-            float3 c = f3(acc.x, acc.y, acc.z) / spp;
-            rgb[3 * i + 0] = (uint8_t)as_u8(sqrtf(c.x) * 255.0f);
-            rgb[3 * i + 1] = (uint8_t)as_u8(sqrtf(c.y) * 255.0f);
-            rgb[3 * i + 2] = (uint8_t)as_u8(sqrtf(c.z) * 255.0f);
+            uint32_t r[4], g[4], b[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) tone_rgb(f3(acc[j].x, acc[j].y, acc[j].z), spp, r[j], g[j], b[j]);
+            if (words && in[0] && in[3]) store_rgb8x4(rgb, p0, r, g, b);
+            else
+                for (int j = 0; j < 4; ++j) if (in[j]) { uint8_t* px = rgb + 3 * (p0 + j); px[0] = (uint8_t)r[j]; px[1] = (uint8_t)g[j]; px[2] = (uint8_t)b[j]; }
         }
     }
 }
@@ -633,26 +806,27 @@ cudaError_t launch_div_verify(float b, float hi, unsigned int* d_mismatches, int
 static dim3 tile_grid(uint32_t w, uint32_t h) { return dim3((w + kTileW - 1) / kTileW, (h + kTileH - 1) / kTileH); }
 
 
-// Tree mode: chunks of at most P.rad_chunk samples; per chunk one persistent trace launch (as many
-// CTAs as fit on the device at once) and one in-order accumulate launch.
-static cudaError_t launch_render_tree(RenderParams P, int sm_count, cudaStream_t stream, uint32_t* launches) {
+// Job-queue modes (tree walk, or the scan with a queue): chunks of at most P.rad_chunk samples; per chunk one
+// persistent trace launch (as many CTAs as fit on the device at once) and one in-order accumulate launch.
+template <class K>
+static cudaError_t launch_queue_chunks(K kernel, size_t smem, RenderParams P, int sm_count, cudaStream_t stream, uint32_t* launches) {
     if (!P.rad || !P.acc || !P.job_counter || P.rad_chunk == 0) return cudaErrorInvalidValue;
     const uint64_t tiles = (uint64_t)((P.width + 7) / 8) * ((P.height + 3) / 4);
     int per_sm = 0;
-    const bool count = P.walk_counters != nullptr;
-    cudaError_t e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_tree_kernel<true>, kBlock, 0)
-                          : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_tree_kernel<false>, kBlock, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlock, smem);
     if (e != cudaSuccess) return e;
-    const int grid = sm_count * (per_sm > 0 ? per_sm : 1);
     const size_t npix = (size_t)P.width * P.height;
     for (uint32_t base = 0; base < P.spp; base += P.rad_chunk) {
         uint32_t k = P.spp - base < P.rad_chunk ? P.spp - base : P.rad_chunk;
         while (tiles * k >= (1ull << 32)) k = (k + 1) / 2;  // batch indices are 32-bit
         P.chunk_base = base; P.chunk_k = k;
+        // no more CTAs than there are batches to draw (a 1-spp 600x600 frame has 11 250)
+        const uint64_t batches = tiles * ((k + kBatchSamples - 1) / kBatchSamples);
+        const uint64_t want = (batches + kBlock / 32 - 1) / (kBlock / 32);
+        const int grid = (int)std::min<uint64_t>((uint64_t)sm_count * (per_sm > 0 ? per_sm : 1), want ? want : 1);
         if ((e = cudaMemsetAsync(P.job_counter, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
-        if (count) render_tree_kernel<true><<<grid, kBlock, 0, stream>>>(P);
-        else render_tree_kernel<false><<<grid, kBlock, 0, stream>>>(P);
-        accumulate_kernel<<<stream_grid(npix, sm_count), 256, 0, stream>>>(P, base == 0, base + k >= P.spp);
+        kernel<<<grid, kBlock, smem, stream>>>(P);
+        accumulate_kernel<<<stream_grid((npix + 3) / 4 + P.height, sm_count), 256, 0, stream>>>(P, base == 0, base + k >= P.spp);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         *launches += 2;
         if (k < P.rad_chunk && base + k < P.spp) base -= P.rad_chunk - k;  // a halved chunk: continue right after it
@@ -662,7 +836,19 @@ static cudaError_t launch_render_tree(RenderParams P, int sm_count, cudaStream_t
 
 cudaError_t launch_render(const RenderParams& P, int sm_count, cudaStream_t stream, uint32_t* launches) {
     *launches = 0;
-    if (P.scene.bvh_nodes) return launch_render_tree(P, sm_count, stream, launches);
+    if (P.scene.bvh_nodes) {
+        if (P.walk_counters) return launch_queue_chunks(render_tree_kernel<true>, 0, P, sm_count, stream, launches);
+        return launch_queue_chunks(render_tree_kernel<false>, 0, P, sm_count, stream, launches);
+    }
+    if (P.queue) {
+        if (P.scene.smem_bytes > 0) {
+            cudaError_t e = cudaFuncSetAttribute(render_queue_kernel<kScanSmem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 P.scene.smem_bytes);
+            if (e != cudaSuccess) return e;
+            return launch_queue_chunks(render_queue_kernel<kScanSmem>, (size_t)P.scene.smem_bytes, P, sm_count, stream, launches);
+        }
+        return launch_queue_chunks(render_queue_kernel<kScanGlobal>, 0, P, sm_count, stream, launches);
+    }
     const dim3 grid = tile_grid(P.width, P.height);
     if (P.scene.smem_bytes > 0) {
         cudaError_t e = cudaFuncSetAttribute(render_kernel<kScanSmem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -734,7 +920,7 @@ static int stream_grid(uint64_t n, int sm_count) {
 cudaError_t launch_tonemap(const float4* sum, uint32_t spp, uint64_t begin, uint64_t end, uint8_t* rgb, int sm_count,
                            cudaStream_t stream) {
     if (end <= begin) return cudaSuccess;
-    tonemap_kernel<<<stream_grid(end - begin, sm_count), 256, 0, stream>>>(sum, (float)spp, begin, end, rgb);
+    tonemap_kernel<<<stream_grid((end - begin) / 4 + 2, sm_count), 256, 0, stream>>>(sum, (float)spp, begin, end, rgb);
     return cudaGetLastError();
 }
 
@@ -744,7 +930,7 @@ cudaError_t launch_reduce_tonemap(const float4* const* peers, int n_peers, uint3
     if (end <= begin) return cudaSuccess;
     PeerPtrs pp{};
     for (int i = 0; i < n_peers; ++i) pp.p[i] = peers[i];
-    reduce_tonemap_kernel<<<stream_grid(end - begin, sm_count), 256, 0, stream>>>(pp, n_peers, (float)spp, begin, end,
+    reduce_tonemap_kernel<<<stream_grid((end - begin) / 4 + 2, sm_count), 256, 0, stream>>>(pp, n_peers, (float)spp, begin, end,
                                                                                   rgb, sum_out);
     return cudaGetLastError();
 }
