@@ -44,7 +44,7 @@ class Stats(ctypes.Structure):
                 ("total_ms", ctypes.c_float), ("gpu_launches", ctypes.c_uint32), ("n_objects", ctypes.c_uint32),
                 ("n_spheres", ctypes.c_uint32), ("n_planes", ctypes.c_uint32), ("n_triangles", ctypes.c_uint32),
                 ("bvh_nodes", ctypes.c_uint32), ("accel_in_use", ctypes.c_uint32), ("sm_count", ctypes.c_uint32),
-                ("sm_clock_khz", ctypes.c_uint32)]
+                ("sm_clock_khz", ctypes.c_uint32), ("reserved", ctypes.c_uint32), ("culled_paths", ctypes.c_uint64)]
 
 
 class WalkStats(ctypes.Structure):
@@ -77,6 +77,9 @@ SYMBOLS = {
     "forma_rt_camera_get": (_int, [_vp, ctypes.POINTER(Camera)]),
     "forma_rt_camera_set": (_int, [_vp, ctypes.POINTER(Camera)]),
     "forma_rt_update": (_int, [_vp, ctypes.c_uint8, ctypes.c_float, _vp]),
+    "forma_rt_flag_error": (_int, [_vp, ctypes.POINTER(_u32)]),
+    "forma_rt_host_alloc": (_int, [_vp, _sz, ctypes.POINTER(_vp)]),
+    "forma_rt_host_free": (_int, [_vp, _vp]),
     "forma_rt_set_partition": (_int, [_vp, _u32, _u32]),
     "forma_rt_accumulate": (_int, [_vp, _u32, _u32, _vp, _vp, ctypes.POINTER(_u32)]),
     "forma_rt_accumulate_reset": (_int, [_vp]),
@@ -174,7 +177,7 @@ def lib() -> ctypes.CDLL:
         for name, (res, args) in {**SYMBOLS, **SYMBOLS_FX, **SYMBOLS_FRAG}.items():
             fn = getattr(L, name)  # AttributeError here = header/library skew
             fn.restype, fn.argtypes = res, args
-        if L.forma_rt_abi_version() != 2:
+        if L.forma_rt_abi_version() != 3:
             raise ImportError("libforma_rt.so ABI version mismatch")
         _lib = L
     return _lib

@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
     const uint32_t x = blockIdx.x * kTileW + lx, y = blockIdx.y * kTileH + ly;
     const bool live = x < P.width && y < P.height;
 
-    uint32_t rays = 0;
+    uint32_t rays = 0, culled = 0;
     float3 col = f3(0.0f, 0.0f, 0.0f);
     if (live) {
         if (P.prior) col = xyz(P.prior[(size_t)x + (size_t)y * P.width]);  // progressive: continue tracer.rs:170-175's sum
@@ -132,6 +132,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
                 }
             }
             rays = P.spp;
+            culled = P.spp;  // reported beside the ray count: these "queries" ran no intersection test
         }
         for (;;) {
             if (!alive) {
@@ -176,6 +177,8 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
     // closest-hit query count: one atomic per warp
     uint32_t wr = __reduce_add_sync(0xffffffffu, rays);
     if (lane == 0 && wr) atomicAdd(P.rays, (unsigned long long)wr);
+    wr = __reduce_add_sync(0xffffffffu, culled);
+    if (lane == 0 && wr) atomicAdd(P.rays + 1, (unsigned long long)wr);
 
     write_out(P, col, x, y, lx, ly, live, tile_rgb);
 }
@@ -966,13 +969,23 @@ __global__ void flag_set_kernel(uint32_t* flag, uint32_t value) {
 
 struct FlagPtrs { const uint32_t* f[kMaxPeers]; };
 
-// one thread per flag spins until its flag has reached `value` (wrap-safe signed distance)
-__global__ void flag_wait_kernel(const __grid_constant__ FlagPtrs p, int n, uint32_t value) {
+// one thread per flag spins until its flag has reached `value` (wrap-safe signed distance) - or until timeout_ns have
+// passed (%globaltimer): a peer that died between frames must not leave this GPU spinning for ever.  A timed-out
+// wait records 1 + the index of its flag in *err (host-mapped) and lets the stream go on; the host side reports it.
+__global__ void flag_wait_kernel(const __grid_constant__ FlagPtrs p, int n, uint32_t value, unsigned long long timeout_ns,
+                                 unsigned int* err) {
     if ((int)threadIdx.x < n) {
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
         uint32_t x;
-        do {
+        for (uint32_t spin = 0;; ++spin) {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(x) : "l"(p.f[threadIdx.x]) : "memory");
-        } while ((int32_t)(x - value) < 0);
+            if ((int32_t)(x - value) >= 0) break;
+            if ((spin & 1023u) == 1023u) {
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > timeout_ns) { if (err) atomicCAS(err, 0u, 1u + threadIdx.x); break; }
+            }
+        }
     }
     __syncthreads();
     __threadfence_system();
@@ -983,11 +996,12 @@ cudaError_t launch_flag_set(uint32_t* flag, uint32_t value, cudaStream_t stream)
     return cudaGetLastError();
 }
 
-cudaError_t launch_flag_wait(const uint32_t* const* flags, int n, uint32_t value, cudaStream_t stream) {
+cudaError_t launch_flag_wait(const uint32_t* const* flags, int n, uint32_t value, unsigned long long timeout_ns,
+                             unsigned int* d_err, cudaStream_t stream) {
     if (n < 1 || n > kMaxPeers) return cudaErrorInvalidValue;
     FlagPtrs pp{};
     for (int i = 0; i < n; ++i) pp.f[i] = flags[i];
-    flag_wait_kernel<<<1, kMaxPeers, 0, stream>>>(pp, n, value);
+    flag_wait_kernel<<<1, kMaxPeers, 0, stream>>>(pp, n, value, timeout_ns, d_err);
     return cudaGetLastError();
 }
 

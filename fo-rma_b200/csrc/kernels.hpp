@@ -30,6 +30,8 @@ cudaError_t launch_mt_finish(const float* acc, uint8_t* out, size_t n, int sm_co
 // stream-ordered flags in peer-visible memory (kernels.cu): *flag = value after everything earlier on `stream` is visible
 // system-wide; later work on `stream` starts once every *flags[i] has reached value (n <= 16)
 cudaError_t launch_flag_set(uint32_t* flag, uint32_t value, cudaStream_t stream);
-cudaError_t launch_flag_wait(const uint32_t* const* flags, int n, uint32_t value, cudaStream_t stream);
+// a wait that times out stores 1 + the flag's index in *d_err (host-mapped, may be null) and lets the stream continue
+cudaError_t launch_flag_wait(const uint32_t* const* flags, int n, uint32_t value, unsigned long long timeout_ns,
+                             unsigned int* d_err, cudaStream_t stream);
 
 }  // namespace forma

@@ -104,6 +104,18 @@ class FusedExchange:
         self.done = [f + 128 for f in peer_flags]
         self.stripe = pixel_stripe(self.rank, self.world, self.npix)
         self.epoch = 0
+        self._opened = [p for r in range(self.world) if r != self.rank
+                        for p in (self.peer_sums[0][r], self.peer_sums[1][r], peer_flags[r])]
+        if self.rank != 0:
+            self._opened.append(self.rgb0)
+
+    def close(self):
+        """Unmap the peers' buffers (forma_rt_ipc_close).  Call on every rank after a final synchronise + barrier: a
+        peer may still be reading this rank's sums until then.  `world` must not exceed the number of GPUs: two
+        ranks on one GPU would spin on each other's flags (the wait gives up after FORMA_RT_FLAG_TIMEOUT_MS)."""
+        for p in self._opened:
+            self.m.ipc_close(p)
+        self._opened = []
 
     def frame(self, spp_per_rank: int, max_depth: int, stream: int) -> int:
         """One frame of spp_per_rank * world samples per pixel; returns kernels launched on this rank."""
@@ -157,7 +169,16 @@ class TileExchange:
         self.done = peer_flags
         self.go = peer_flags[0] + 128
         self.epoch = 0
+        self._opened = [p for r, p in enumerate(peer_flags) if r != self.rank] + ([self.rgb0] if self.rank != 0 else [])
         model.set_partition(self.rank, self.world)
+
+    def close(self):
+        """Unmap the peers' buffers and give the handle its whole frame back (partition (0, 1)).  Call on every rank
+        after a final synchronise + barrier."""
+        for p in self._opened:
+            self.m.ipc_close(p)
+        self._opened = []
+        self.m.set_partition(0, 1)
 
     def frame(self, spp: int, max_depth: int, stream: int) -> int:
         m = self.m

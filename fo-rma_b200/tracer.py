@@ -264,6 +264,21 @@ class TraceModel:
     def synchronize(self):
         check(_lib.lib().forma_rt_synchronize(self._h))
 
+    def flag_error(self) -> int:
+        """0, or 1 + the index of the flag a flag_wait_device of this handle gave up on (raises FormaError then)."""
+        n = ctypes.c_uint32(0)
+        check(_lib.lib().forma_rt_flag_error(self._h, ctypes.byref(n)))
+        return n.value
+
+    def host_alloc(self, nbytes: int) -> np.ndarray:
+        """Page-locked host buffer owned by the handle, as a uint8 array (a `pixels` buffer at the pinned D2H rate)."""
+        p = ctypes.c_void_p()
+        check(_lib.lib().forma_rt_host_alloc(self._h, nbytes, ctypes.byref(p)))
+        return np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(ctypes.c_uint8)), shape=(nbytes,))
+
+    def host_free(self, buf: np.ndarray) -> None:
+        check(_lib.lib().forma_rt_host_free(self._h, buf.ctypes.data))
+
 
 def create_model(width: int, height: int, **kw) -> TraceModel:
     """tracer::create_model (tracer.rs:19-28)."""

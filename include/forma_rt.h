@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FORMA_RT_ABI_VERSION 2
+#define FORMA_RT_ABI_VERSION 3
 
 /* error codes */
 #define FORMA_RT_OK 0
@@ -102,6 +102,9 @@ typedef struct forma_rt_stats {
     uint32_t accel_in_use;  /* FORMA_RT_ACCEL_BRUTE | FORMA_RT_ACCEL_LBVH */
     uint32_t sm_count;
     uint32_t sm_clock_khz;  /* cudaDevAttrClockRate */
+    uint32_t reserved;
+    uint64_t culled_paths;  /* paths of `rays` that ran NO intersection test: every sample of a pixel whose whole primary
+                               beam misses the scene's bounding sphere goes camera ray -> sky (ABI 3) */
 } forma_rt_stats;
 
 /* forma_rt_walk_stats: what one frame's LBVH traversal touches (SURVEY 8(d), config D's L2 roofline) */
@@ -221,10 +224,15 @@ FORMA_RT_API int forma_rt_reduce_tonemap_device(forma_rt* ctx, const void* const
  * across GPUs without host-side barriers.  A flag is a zero-initialised uint32 in a forma_rt_device_alloc'ed buffer that
  * the peers map through forma_rt_ipc_open.  set: once everything queued on `stream` before the call is complete and
  * visible system-wide, *d_flag = value.  wait: work queued on `stream` after the call starts only when every
- * *d_flags[i] has reached `value` (n <= 16; values only grow; comparison is wrap-safe). */
+ * *d_flags[i] has reached `value` (n <= 16; values only grow; comparison is wrap-safe).
+ * A wait never spins for ever: after FORMA_RT_FLAG_TIMEOUT_MS (environment, default 30 000) it gives up, lets the
+ * stream go on and records the flag; the next forma_rt_flag_wait_device / forma_rt_synchronize / forma_rt_flag_error of
+ * the handle fails with FORMA_RT_ECUDA and names it (a peer rank died between frames, or two ranks share one GPU -
+ * `world` must not exceed the number of GPUs).  forma_rt_flag_error reports 0 or 1 + the index of that flag. */
 FORMA_RT_API int forma_rt_flag_set_device(forma_rt* ctx, void* d_flag, uint32_t value, void* stream);
 FORMA_RT_API int forma_rt_flag_wait_device(forma_rt* ctx, const void* const* d_flags, uint32_t n, uint32_t value,
                                            void* stream);
+FORMA_RT_API int forma_rt_flag_error(forma_rt* ctx, uint32_t* flag_index_plus_one);
 
 FORMA_RT_API int forma_rt_ipc_export(forma_rt* ctx, void* d_ptr, uint8_t handle[64]);
 FORMA_RT_API int forma_rt_ipc_open(forma_rt* ctx, const uint8_t handle[64], void** d_ptr);
@@ -233,6 +241,11 @@ FORMA_RT_API int forma_rt_ipc_close(forma_rt* ctx, void* d_ptr);
 FORMA_RT_API int forma_rt_device_alloc(forma_rt* ctx, size_t bytes, void** d_ptr); /* zero-filled */
 FORMA_RT_API int forma_rt_device_free(forma_rt* ctx, void* d_ptr);
 FORMA_RT_API int forma_rt_synchronize(forma_rt* ctx);
+/* page-locked host memory owned by the handle (freed by forma_rt_destroy): a `pixels` buffer (TraceModel.pixels,
+ * tracer.rs:16) allocated here makes forma_rt_update / forma_rt_render copy the frame at the pinned D2H rate - the
+ * rate bench.py's e2e figure is quoted at; any other host buffer works too, through a staged copy. */
+FORMA_RT_API int forma_rt_host_alloc(forma_rt* ctx, size_t bytes, void** h_ptr);
+FORMA_RT_API int forma_rt_host_free(forma_rt* ctx, void* h_ptr);
 
 /* ---- misc -------------------------------------------------------------------------------------- */
 /* Instrumented (untimed) frame: the same traversal as forma_rt_render(spp, 0, max_depth) with per-lane counters,

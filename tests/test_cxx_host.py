@@ -35,7 +35,7 @@ def test_plain_c_program_reads_back_what_the_python_mirror_reads(built):
     out = subprocess.run([os.path.join(built, "abi_check")], capture_output=True, text=True)
     assert out.returncode == 0, out.stderr
     lines = out.stdout.splitlines()
-    assert lines[0] == "abi 2"
+    assert lines[0] == "abi 3"
     m = forma_b200.create_model(64, 48, flags=_lib.HOST_ONLY)
     for which in range(3):
         m.scene.load_builtin(which)

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     L = _lib.lib()
     for name in declared:
         assert hasattr(L, name), name
-    assert L.forma_rt_abi_version() == 2
+    assert L.forma_rt_abi_version() == 3
 
 
 def test_no_cpu_fallback_render_fails_loudly_without_device():

@@ -11,9 +11,11 @@ def gen(n):
     mod = importlib.util.module_from_spec(spec); spec.loader.exec_module(mod)
     return json.dumps(mod.generate(n))
 
-def run(name, txt, w, h, spp, accel, builtin=None, reps=3):
+def run(name, txt, w, h, spp, accel, builtin=None, reps=3, orbit=False):
     m = forma_b200.create_model(w, h, seed=0, accel=accel)
-    if builtin is not None: m.scene.load_builtin(builtin)
+    if builtin is not None:
+        m.scene.load_builtin(builtin)
+        if orbit: m.scene.camera.orbit((0.0, 0.0, 0.0))  # the frontend's first update(): eye to (5, 0, 0) (camera.rs:97-102, Q12)
     else:
         m.scene.load_json(txt); m.scene.camera.use_json()
     best = None
@@ -27,20 +29,22 @@ def run(name, txt, w, h, spp, accel, builtin=None, reps=3):
     m.close()
 
 S = os.path.join(ROOT, "tests", "golden", "scenes")
-which = sys.argv[1:] or ["C", "A", "B", "D", "builtin"]
+AUTO_ONLY = "--auto" in sys.argv  # skip the brute-force runs of A / B (slow, only a reference point)
+which = [a for a in sys.argv[1:] if not a.startswith("--")] or ["C", "A", "B", "D", "builtin"]
 if "C" in which:
     t = open(os.path.join(S, "scene_09.json")).read()
     for a in (_lib.ACCEL_BRUTE, _lib.ACCEL_AUTO): run("C scene_09 1080p 256spp", t, 1920, 1080, 256, a)
 if "A" in which:
     t = open(os.path.join(S, "scene_01.json")).read()
-    for a in (_lib.ACCEL_BRUTE, _lib.ACCEL_AUTO): run("A scene_01 600x600 50spp", t, 600, 600, 50, a)
+    for a in ((_lib.ACCEL_AUTO,) if AUTO_ONLY else (_lib.ACCEL_BRUTE, _lib.ACCEL_AUTO)): run("A scene_01 600x600 50spp", t, 600, 600, 50, a)
     run("A' scene_01 1080p 16spp", t, 1920, 1080, 16, _lib.ACCEL_AUTO)
 if "B" in which:
     t = open(os.path.join(S, "scene_05.json")).read()
-    for a in (_lib.ACCEL_BRUTE, _lib.ACCEL_AUTO): run("B' scene_05 1080p 4spp", t, 1920, 1080, 4, a)
+    for a in ((_lib.ACCEL_AUTO,) if AUTO_ONLY else (_lib.ACCEL_BRUTE, _lib.ACCEL_AUTO)): run("B' scene_05 1080p 4spp", t, 1920, 1080, 4, a)
 if "builtin" in which:
     for b in (0, 2):
-        for a in (_lib.ACCEL_BRUTE, _lib.ACCEL_AUTO): run(f"builtin{b} 1080p 64spp", None, 1920, 1080, 64, a, builtin=b)
+        run(f"builtin{b} 1080p 64spp", None, 1920, 1080, 64, _lib.ACCEL_AUTO, builtin=b)
+        run(f"builtin{b} 600x600 50spp after update()", None, 600, 600, 50, _lib.ACCEL_AUTO, builtin=b, orbit=True)
 if "D" in which:
     t = gen(100_000)
     run("D 100k spheres 1080p 16spp", t, 1920, 1080, 16, _lib.ACCEL_AUTO, reps=2)
