@@ -18,6 +18,7 @@ OK, EINVAL, EJSON, ECUDA, EIO, ENOMEM = 0, -1, -2, -3, -4, -5
 NO_JITTER, PINHOLE, HOST_ONLY, SRGB_OUT = 1, 2, 4, 8
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_LBVH = 0, 1, 2
 SPHERE, PLANE, TRIANGLE = 0, 1, 2
+NOALLOC_MAX_PIXELS = 262144  # FORMA_RT_NOALLOC_MAX_PIXELS
 
 
 class Options(ctypes.Structure):
@@ -80,6 +81,7 @@ SYMBOLS = {
     "forma_rt_flag_error": (_int, [_vp, ctypes.POINTER(_u32)]),
     "forma_rt_host_alloc": (_int, [_vp, _sz, ctypes.POINTER(_vp)]),
     "forma_rt_host_free": (_int, [_vp, _vp]),
+    "forma_rt_render_device_noalloc": (_int, [_vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "forma_rt_set_partition": (_int, [_vp, _u32, _u32]),
     "forma_rt_accumulate": (_int, [_vp, _u32, _u32, _vp, _vp, ctypes.POINTER(_u32)]),
     "forma_rt_accumulate_reset": (_int, [_vp]),

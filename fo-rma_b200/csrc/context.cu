@@ -1163,3 +1163,46 @@ int forma_rt_save_image_mt(forma_rt* ctx, uint32_t sample, const char* path) {
 }
 
 }  // extern "C"
+
+// include/forma_rt.h: forma_rt_render_device without a single allocation (no counterpart in the reference).
+// Everything that allocates must have happened before: the scene upload, the
+// LBVH build and the one-off div_const check are done by any earlier render call of the handle.
+extern "C" int forma_rt_render_device_noalloc(forma_rt* ctx, uint32_t spp, uint32_t sample_offset, uint32_t max_depth,
+                                              void* d_rgb, void* d_sum_rgba, void* stream) {
+    NEED_DEV(ctx);
+    if (spp == 0) return fail(FORMA_RT_EINVAL, "forma_rt_render_device_noalloc: spp must be >= 1");
+    if (max_depth > (uint32_t)forma::kMaxDepthCap)
+        return fail(FORMA_RT_EINVAL, "forma_rt_render_device_noalloc: max_depth exceeds the attenuation stack (64; the reference uses 50)");
+    if (!d_rgb && !d_sum_rgba) return fail(FORMA_RT_EINVAL, "forma_rt_render_device_noalloc: no output buffer");
+    const uint64_t npix = (uint64_t)ctx->width * ctx->height;
+    if (npix > (uint64_t)FORMA_RT_NOALLOC_MAX_PIXELS)
+        return fail(FORMA_RT_EINVAL, "forma_rt_render_device_noalloc: " + std::to_string(ctx->width) + " x " + std::to_string(ctx->height) +
+                    " = " + std::to_string(npix) + " pixels exceed the static scratch (FORMA_RT_NOALLOC_MAX_PIXELS = " +
+                    std::to_string(FORMA_RT_NOALLOC_MAX_PIXELS) + "); use forma_rt_render_device");
+    if (ctx->scene_dirty || ctx->fast_div < 0)
+        return fail(FORMA_RT_EINVAL, "forma_rt_render_device_noalloc: the scene is not resident on the device yet (uploading it "
+                    "allocates): call forma_rt_render / forma_rt_render_device once after every scene change first");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    forma::RenderParams P{};
+    P.cam = ctx->scene.camera.c;
+    P.scene = ctx->view;
+    P.width = ctx->width; P.height = ctx->height;
+    P.spp = spp; P.sample_offset = sample_offset; P.max_depth = max_depth; P.flags = ctx->flags;
+    P.rk.expand(ctx->seed);
+    P.rgb = (uint8_t*)d_rgb; P.sum = (float4*)d_sum_rgba; P.rays = ctx->d_rays;
+    P.part_mod = ctx->part_mod; P.part_rem = ctx->part_rem;
+    P.part_pitch = (ctx->width + 31) / 32;
+    while (std::gcd(P.part_pitch, P.part_mod) != 1u) ++P.part_pitch;
+    P.refill = ctx->refill; P.leaf_batch = ctx->leaf_batch;
+    P.inv_w = 1.0f / (float)ctx->width; P.inv_h = 1.0f / (float)ctx->height;
+    P.fast_div = (uint32_t)ctx->fast_div;
+    uint32_t launches = 0;
+    CU_TRY(cudaMemsetAsync(ctx->d_rays, 0, 2 * sizeof(unsigned long long), s));
+    CU_TRY(cudaEventRecord(ctx->ev_k0, s));
+    CU_TRY(forma::launch_render_noalloc(P, ctx->device, ctx->sm_count, s, &launches));
+    CU_TRY(cudaEventRecord(ctx->ev_k1, s));
+    ctx->stats.gpu_launches = launches;
+    ctx->stats.paths = npix * spp;  // under forma_rt_set_partition: an upper bound (the handle's own tiles only are traced)
+    ctx->stats_pending = true;
+    return FORMA_RT_OK;
+}

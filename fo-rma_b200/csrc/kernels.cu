@@ -1005,4 +1005,44 @@ cudaError_t launch_flag_wait(const uint32_t* const* flags, int n, uint32_t value
     return cudaGetLastError();
 }
 
+// ---- no-allocation variant of the job-queue launch (forma_rt_render_device_noalloc; no counterpart in the
+// reference: added for callers that cannot call cudaMalloc - code under CUDA
+// graph capture, tight serving loops).  The scratch of render_tree_kernel / render_queue_kernel + accumulate_kernel
+// - the job counter, the per-path radiance `rad`, the cross-chunk sum `acc` - lives in ONE file-scope device array
+// of a fixed, modest size instead of the handle's cudaMalloc'ed buffers:
+//     [0, 256)                         job counter (cleared per chunk by the launcher)
+//     [256, 256 + 4 MiB)               rad: kNoAllocSlots float4 path slots
+//     [256 + 4 MiB, 256 + 8 MiB)       acc: kNoAllocSlots float4 pixels
+// = 8 MiB + 256 B held by every GPU that loads the library, until exit.  Every call shares it and it keeps the
+// last call's contents: the job counter is cleared before every launch, every rad / acc slot a launch reads has
+// been written by that launch first, so nothing else needs to start at zero - but two calls that overlap on the
+// GPU (two streams, two handles, two threads) RACE on it.  The array's name is only a host-side stand-in: the device
+// address comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr size_t kNoAllocSlots = FORMA_RT_NOALLOC_MAX_PIXELS;
+constexpr size_t kNoAllocBytes = 256 + 2 * kNoAllocSlots * sizeof(float4);
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+cudaError_t launch_render_noalloc(RenderParams P, int device, int sm_count, cudaStream_t stream, uint32_t* launches) {
+    *launches = 0;
+    static void* base_of_device[64] = {};
+    if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+    if (!base_of_device[device]) {  // set-up, once per device; the caller has made `device` current
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        base_of_device[device] = p;
+    }
+    const size_t npix = (size_t)P.width * P.height;
+    if (npix == 0 || npix > kNoAllocSlots) return cudaErrorInvalidValue;  // the entry point reports this with the limit
+    unsigned char* base = static_cast<unsigned char*>(base_of_device[device]);
+    P.job_counter = reinterpret_cast<unsigned int*>(base);
+    P.rad = reinterpret_cast<float4*>(base + 256);
+    P.acc = reinterpret_cast<float4*>(base + 256 + kNoAllocSlots * sizeof(float4));
+    const size_t chunk = kNoAllocSlots / npix;  // samples of the frame that fit the radiance slots (>= 1)
+    P.rad_chunk = (uint32_t)(chunk < 64 ? chunk : 64);
+    if (P.rad_chunk > P.spp) P.rad_chunk = P.spp;
+    if (!P.scene.bvh_nodes) P.queue = 1u;  // scanned scenes: the job-queue scan kernel is the one with scratch
+    return launch_render(P, sm_count, stream, launches);
+}
+
 }  // namespace forma

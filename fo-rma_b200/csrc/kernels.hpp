@@ -13,6 +13,9 @@ cudaError_t launch_div_verify(float b, float hi, unsigned int* d_mismatches, int
 // color_utils::srgb_encode (color_utils.rs:49-66) in place on nbytes of RGB8; lut = the u8 -> u8 map
 cudaError_t launch_srgb_encode(uint8_t* rgb, size_t nbytes, const uint8_t lut[256], int sm_count, cudaStream_t stream);
 cudaError_t launch_primary_hits(const PrimaryParams& P, cudaStream_t stream);
+// launch_render's job-queue path with its scratch in a file-scope static device array (kernels.cu): allocates nothing.
+// width * height <= FORMA_RT_NOALLOC_MAX_PIXELS; `device` = the current device (per-device symbol address cache)
+cudaError_t launch_render_noalloc(RenderParams P, int device, int sm_count, cudaStream_t stream, uint32_t* launches);
 cudaError_t launch_tonemap(const float4* sum, uint32_t spp, uint64_t begin, uint64_t end, uint8_t* rgb, int sm_count,
                            cudaStream_t stream);
 cudaError_t launch_reduce_tonemap(const float4* const* peers, int n_peers, uint32_t spp, uint64_t begin, uint64_t end,

@@ -229,6 +229,11 @@ class TraceModel:
     def render_device(self, spp, sample_offset, max_depth, d_rgb: int | None, d_sum: int | None, stream: int = 0):
         check(_lib.lib().forma_rt_render_device(self._h, spp, sample_offset, max_depth, d_rgb, d_sum, stream or None))
 
+    def render_device_noalloc(self, spp, sample_offset, max_depth, d_rgb: int | None, d_sum: int | None, stream: int = 0):
+        """render_device without any allocation (static device scratch; width * height <= _lib.NOALLOC_MAX_PIXELS, the
+        scene resident from an earlier render call).  Calls that overlap on one GPU race on the scratch."""
+        check(_lib.lib().forma_rt_render_device_noalloc(self._h, spp, sample_offset, max_depth, d_rgb, d_sum, stream or None))
+
     def tonemap_device(self, d_sum: int, spp_total: int, d_rgb: int, pixel_begin=0, pixel_end=None, stream: int = 0):
         pixel_end = self.width * self.height if pixel_end is None else pixel_end
         check(_lib.lib().forma_rt_tonemap_device(self._h, d_sum, spp_total, pixel_begin, pixel_end, d_rgb, stream or None))

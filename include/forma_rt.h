@@ -208,6 +208,20 @@ FORMA_RT_API int forma_rt_set_partition(forma_rt* ctx, uint32_t rank, uint32_t w
  * synchronising it.  d_sum_rgba: width*height float4 (nullable).  d_rgb: width*height*3 bytes (nullable). */
 FORMA_RT_API int forma_rt_render_device(forma_rt* ctx, uint32_t spp, uint32_t sample_offset, uint32_t max_depth, void* d_rgb,
                            void* d_sum_rgba, void* stream);
+/* forma_rt_render_device WITHOUT ANY ALLOCATION.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same results (bit-identical sums, bytes and ray count).  The scratch of the
+ * job-queue kernels (per-path radiance, cross-chunk sum, job counter) lives in a file-scope static device array of
+ * 8 MiB + 256 B that every GPU loading the library holds until exit, so
+ *   - width * height must not exceed FORMA_RT_NOALLOC_MAX_PIXELS (else FORMA_RT_EINVAL; any spp is fine);
+ *   - the scene must already be resident: one forma_rt_render / forma_rt_render_device after every scene change
+ *     (the upload and the LBVH build allocate), else FORMA_RT_EINVAL;
+ *   - all calls on a GPU share the array, which keeps the last call's contents (everything a launch reads it has
+ *     cleared or written first): calls that OVERLAP on the GPU - two streams, two handles, two threads - race.
+ * The call itself makes no cudaMalloc / cudaFree / allocating library call; the caller owns d_rgb / d_sum_rgba. */
+#define FORMA_RT_NOALLOC_MAX_PIXELS 262144 /* 2^18, e.g. 512 x 512 or 640 x 400 */
+FORMA_RT_API int forma_rt_render_device_noalloc(forma_rt* ctx, uint32_t spp, uint32_t sample_offset, uint32_t max_depth,
+                                               void* d_rgb, void* d_sum_rgba, void* stream);
 /* tracer.rs:177-184 on a summed buffer: rgb = as_u8(sqrt(sum / spp_total) * 255), pixels
  * [pixel_begin, pixel_end).  Used after the cross-GPU reduce of the per-rank sums. */
 FORMA_RT_API int forma_rt_tonemap_device(forma_rt* ctx, const void* d_sum_rgba, uint32_t spp_total, uint64_t pixel_begin,
