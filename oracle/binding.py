@@ -16,6 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "liboracle.so")
 
 FLAG_NO_JITTER, FLAG_PINHOLE, FLAG_SEQ_RNG, FLAG_MT_ROWS = 1, 2, 4, 8
+FLAG_BVH = 16  # checker-side accelerator (forma_oracle.cpp OBvh): the scan's results, plane-free finite lists only
 CAMERA_FLOATS = 26
 # field offsets (in floats) inside the 26-float camera block
 CAM_FIELDS = {

@@ -34,6 +34,7 @@
 #include <limits>
 #include <thread>
 #include <vector>
+#include <algorithm>
 #include <atomic>
 
 namespace {
@@ -495,11 +496,171 @@ void camera_orbit(Camera& c, Vec3 delta) {  // camera.rs:97-122
 // ----------------------------------------------------------------------------------------------
 // get_color — cpu_ray_tracer/tracer.rs:189-219 (recursive, shared HitRecord across the scan)
 // ----------------------------------------------------------------------------------------------
+struct OBvh;
 struct Trace {
     const Object* objects;
     size_t n;
     uint32_t max_depth;  // tracer.rs:10 MAX_DEPTH = 50 (u8)
+    const OBvh* bvh = nullptr;  // checker-side accelerator (below); nullptr = the reference's scan
 };
+
+// ----------------------------------------------------------------------------------------------
+// CHECKER-SIDE ACCELERATOR (no reference counterpart: tracer.rs:195-200 scans every object; shapes/aabb.rs is a
+// stub).  Exists so that config D (100 000 spheres) can be checked at its full frame size: the brute-force scan
+// costs O(n) per ray.  It returns EXACTLY what the scan returns and shares nothing with the product's LBVH:
+//   * own tree: top-down median split of the centroid bounds, leaves of <= 4 primitives, boxes in double;
+//   * the scan accepts object i iff its candidate t (sphere.rs:30-41: root_one if it exceeds t_min, else root_two;
+//     the triangle's t) lies in (t_min, closest_so_far), so it ends with the lexicographic minimum of (t, i) over
+//     all objects that have a candidate - which is what the walk keeps, in any visiting order - and with that
+//     object's HitRecord, since a sphere / triangle only writes the record when it accepts;
+//   * a node is skipped only when its box, grown by more than the distance at which sphere.rs:25-29's f32
+//     discriminant can still turn positive for a true miss (~16 u |o - c|^2 / r, u = 2^-24; here 2^-18 (dist to the
+//     box + its diagonal)^2 / r_min of the node, evaluated per node in double) plus 2^-12 of the scene scale for the
+//     triangle test, is missed by the ray or entered beyond the best t so far.
+// Only used when the list holds no plane (Plane::hit is order-sensitive, Q4 / Q5) and every coordinate is finite;
+// tests/test_oracle_bvh.py checks it against the scan bit for bit before anything relies on it.
+// ----------------------------------------------------------------------------------------------
+struct OBvhNode {
+    double lo[3], hi[3];
+    double inv_rmin;       // largest 1 / |radius| below this node (0: triangles only)
+    int left, right;       // children, or (first, -count) of a leaf's slice of `order`
+};
+struct OBvh {
+    std::vector<OBvhNode> nodes;
+    std::vector<uint32_t> order;  // primitive (list) indices, leaf slices contiguous
+    double scale = 0.0;
+};
+
+inline void prim_box(const Object& o, double lo[3], double hi[3], double* inv_r) {
+    if (o.kind == 0) {
+        const double r = std::fabs((double)o.b[0]);
+        for (int k = 0; k < 3; ++k) { lo[k] = (double)o.a[k] - r; hi[k] = (double)o.a[k] + r; }
+        *inv_r = 1.0 / r;
+    } else {
+        for (int k = 0; k < 3; ++k) {
+            lo[k] = std::min({(double)o.a[k], (double)o.b[k], (double)o.c[k]});
+            hi[k] = std::max({(double)o.a[k], (double)o.b[k], (double)o.c[k]});
+        }
+        *inv_r = 0.0;
+    }
+}
+
+int obvh_build(OBvh& B, const Object* objs, uint32_t first, uint32_t count) {
+    OBvhNode nd;
+    double clo[3] = {1e300, 1e300, 1e300}, chi[3] = {-1e300, -1e300, -1e300};
+    for (int k = 0; k < 3; ++k) { nd.lo[k] = 1e300; nd.hi[k] = -1e300; }
+    nd.inv_rmin = 0.0;
+    for (uint32_t i = first; i < first + count; ++i) {
+        double lo[3], hi[3], q;
+        prim_box(objs[B.order[i]], lo, hi, &q);
+        nd.inv_rmin = std::max(nd.inv_rmin, q);
+        for (int k = 0; k < 3; ++k) {
+            nd.lo[k] = std::min(nd.lo[k], lo[k]); nd.hi[k] = std::max(nd.hi[k], hi[k]);
+            const double c = 0.5 * (lo[k] + hi[k]);
+            clo[k] = std::min(clo[k], c); chi[k] = std::max(chi[k], c);
+        }
+    }
+    const int id = (int)B.nodes.size();
+    B.nodes.push_back(nd);
+    int axis = 0;
+    for (int k = 1; k < 3; ++k) if (chi[k] - clo[k] > chi[axis] - clo[axis]) axis = k;
+    if (count <= 4 || !(chi[axis] > clo[axis])) {
+        B.nodes[id].left = (int)first; B.nodes[id].right = -(int)count;
+        return id;
+    }
+    const uint32_t mid = first + count / 2;
+    auto centre = [&](uint32_t p) {
+        double lo[3], hi[3], q;
+        prim_box(objs[p], lo, hi, &q);
+        return lo[axis] + hi[axis];
+    };
+    std::nth_element(B.order.begin() + first, B.order.begin() + mid, B.order.begin() + first + count,
+                     [&](uint32_t x, uint32_t y) { const double cx = centre(x), cy = centre(y); return cx < cy || (cx == cy && x < y); });
+    const int l = obvh_build(B, objs, first, mid - first);
+    const int r = obvh_build(B, objs, mid, first + count - mid);
+    B.nodes[id].left = l; B.nodes[id].right = r;
+    return id;
+}
+
+// false: the list cannot be accelerated exactly (a plane, or non-finite data) - the caller scans
+bool obvh_make(OBvh& B, const Object* objs, size_t n) {
+    if (n < 2 || n > 0x7fffffffu) return false;
+    B.order.resize(n);
+    for (size_t i = 0; i < n; ++i) {
+        const Object& o = objs[i];
+        if (o.kind != 0 && o.kind != 2) return false;
+        double lo[3], hi[3], q;
+        prim_box(o, lo, hi, &q);
+        for (int k = 0; k < 3; ++k) {
+            if (!std::isfinite(lo[k]) || !std::isfinite(hi[k])) return false;
+            B.scale = std::max({B.scale, std::fabs(lo[k]), std::fabs(hi[k])});
+        }
+        if (o.kind == 0 && !std::isfinite(q)) return false;
+        B.order[i] = (uint32_t)i;
+    }
+    B.nodes.reserve(n);
+    obvh_build(B, objs, 0, (uint32_t)n);
+    return true;
+}
+
+// entry parameter of the ray into the padded box, or -1 when it misses it (or enters beyond `best`)
+inline double obvh_entry(const OBvh& B, const OBvhNode& nd, const double o[3], const double d[3], double best) {
+    double dist2 = 0.0, diag2 = 0.0;
+    for (int k = 0; k < 3; ++k) {
+        const double c = 0.5 * (nd.lo[k] + nd.hi[k]), h = 0.5 * (nd.hi[k] - nd.lo[k]);
+        dist2 += (o[k] - c) * (o[k] - c); diag2 += h * h;
+    }
+    const double reach = std::sqrt(dist2) + std::sqrt(diag2);
+    const double pad = 3.814697265625e-06 * reach * reach * nd.inv_rmin + 2.44140625e-4 * B.scale + 1e-30;  // 2^-18, 2^-12
+    double t0 = 0.0, t1 = best;
+    for (int k = 0; k < 3; ++k) {
+        const double lo = nd.lo[k] - pad, hi = nd.hi[k] + pad;
+        if (d[k] == 0.0) { if (o[k] < lo || o[k] > hi) return -1.0; continue; }
+        double a = (lo - o[k]) / d[k], b = (hi - o[k]) / d[k];
+        if (a > b) std::swap(a, b);
+        t0 = std::max(t0, a); t1 = std::min(t1, b);
+    }
+    if (!(t0 <= t1 * (1.0 + 1e-9) + 1e-9)) return -1.0;
+    return t0;
+}
+
+// the scan of tracer.rs:195-200 over a plane-free list: winner index (or -1), its record and t
+bool object_hit(const Object& o, Ray ray, float t_min, float t_max, HitRecord* rec);
+int obvh_closest(const OBvh& B, const Object* objs, Ray ray, float t_min, HitRecord* rec_out, float* t_out) {
+    const double o[3] = {ray.from.x, ray.from.y, ray.from.z}, d[3] = {ray.to.x, ray.to.y, ray.to.z};
+    int best = -1;
+    float best_t = std::numeric_limits<float>::max();
+    int stack[128];
+    int sp = 0;
+    stack[sp++] = 0;
+    while (sp > 0) {
+        const OBvhNode& nd = B.nodes[stack[--sp]];
+        if (obvh_entry(B, nd, o, d, (double)best_t) < 0.0) continue;
+        if (nd.right < 0) {
+            for (int i = nd.left; i < nd.left - nd.right; ++i) {
+                const int p = (int)B.order[i];
+                HitRecord rec;
+                // the candidate does not depend on t_max (see above): ask with the widest range, compare here
+                if (object_hit(objs[p], ray, t_min, std::numeric_limits<float>::max(), &rec) &&
+                    (rec.t < best_t || (rec.t == best_t && p < best))) {
+                    best_t = rec.t; best = p; *rec_out = rec;
+                }
+            }
+            continue;
+        }
+        // nearer child last on the stack = first off it
+        const double el = obvh_entry(B, B.nodes[nd.left], o, d, (double)best_t);
+        const double er = obvh_entry(B, B.nodes[nd.right], o, d, (double)best_t);
+        if (sp + 2 > 128) return -2;  // cannot happen for a median-split tree over < 2^31 primitives
+        if (el >= 0.0 && er >= 0.0) {
+            if (el <= er) { stack[sp++] = nd.right; stack[sp++] = nd.left; }
+            else { stack[sp++] = nd.left; stack[sp++] = nd.right; }
+        } else if (el >= 0.0) stack[sp++] = nd.left;
+        else if (er >= 0.0) stack[sp++] = nd.right;
+    }
+    *t_out = best_t;
+    return best;
+}
 
 Vec3 get_color(Ray ray, const Trace& tr, uint32_t depth) {
     g_rng->rays++;
@@ -507,6 +668,10 @@ Vec3 get_color(Ray ray, const Trace& tr, uint32_t depth) {
     const float t_min = 0.001f;
     float closest_so_far = std::numeric_limits<float>::max();
     const Object* temp_obj = nullptr;
+    if (tr.bvh) {  // checker-side accelerator: the same winner and record as the scan below
+        const int w = obvh_closest(*tr.bvh, tr.objects, ray, t_min, &hit_record, &closest_so_far);
+        if (w >= 0) temp_obj = &tr.objects[w];
+    } else
     for (size_t i = 0; i < tr.n; ++i) {
         const Object& obj = tr.objects[i];
         if (object_hit(obj, ray, t_min, closest_so_far, &hit_record)) {
@@ -535,7 +700,7 @@ inline uint8_t as_u8(float f) {
     return (uint8_t)(int)f;
 }
 
-enum : uint32_t { FLAG_NO_JITTER = 1, FLAG_PINHOLE = 2, FLAG_SEQ_RNG = 4, FLAG_MT_ROWS = 8 };
+enum : uint32_t { FLAG_NO_JITTER = 1, FLAG_PINHOLE = 2, FLAG_SEQ_RNG = 4, FLAG_MT_ROWS = 8, FLAG_BVH = 16 };
 
 }  // namespace
 
@@ -688,6 +853,8 @@ uint64_t oracle_render(const Object* objs, uint64_t n, const Camera* cam, uint32
     if (y1 > height) y1 = height;
     std::atomic<uint64_t> total_rays{0};
     Trace tr{objs, (size_t)n, max_depth};
+    OBvh bvh;  // FLAG_BVH: the checker-side accelerator when the list allows it, else the scan as always
+    if ((flags & FLAG_BVH) && obvh_make(bvh, objs, (size_t)n)) tr.bvh = &bvh;
     auto worker = [&](uint32_t tid) {
         RngCtx ctx;
         ctx.mode = (flags & FLAG_SEQ_RNG) ? 1 : 0;

@@ -174,3 +174,38 @@ def test_stream_ordered_flags():
         m.flag_wait_device([], 1)
     with pytest.raises(forma_b200.tracer.FormaError):
         m.flag_set_device(flag_a + 1, 1)
+
+
+def test_config_e_4k_sample_ranges_and_reduce_vs_oracle():
+    """BASELINE config E's per-GPU unit of work - scene_09 at 3840x2160, 512 spp of a sample range - for two ranks'
+    ranges [0, 512) and [512, 1024), then the exchange step (rank-order sum + tone-map, forma_rt_reduce_tonemap_device)
+    - against the oracle on a two-row band through the tetrahedron: per-range f32 sums bit for bit, and the RGB8 band
+    of the reduced frame equal to the oracle's tone-map (tracer.rs:177-184) of the same rank-order sum."""
+    import torch
+    w, h, spp = 3840, 2160, 512
+    txt, objs, cam = load_scene_pair("scene_09", w, h)
+    m = forma_b200.create_model(w, h, seed=0)
+    m.scene.load_json(txt)
+    m.scene.camera.use_json()
+    ids, _ = m.primary_hits()
+    ys = np.nonzero((ids >= 0).any(axis=1))[0]
+    y0 = int(ys[len(ys) // 2])
+    dev = torch.device("cuda", 0)
+    npix = w * h
+    parts = [torch.zeros((npix, 4), dtype=torch.float32, device=dev) for _ in range(2)]
+    rgb = torch.zeros(npix * 3, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    for r, p in enumerate(parts):
+        m.render_device(spp, r * spp, 50, None, p.data_ptr(), stream)
+    m.reduce_tonemap_device([p.data_ptr() for p in parts], 2 * spp, 0, npix, rgb.data_ptr(), None, stream)
+    torch.cuda.synchronize()
+    band = slice(y0 * w, (y0 + 2) * w)
+    lin_o = []
+    for r in range(2):
+        _, lo, _ = ob.render(objs, cam, w, h, spp, sample_offset=r * spp, seed=0, y0=y0, y1=y0 + 2, nthreads=16, want_rgb=False)
+        lin_o.append(lo[y0:y0 + 2].reshape(-1, 3))
+        assert np.array_equal(bits(parts[r][band, :3].cpu().numpy()), bits(lin_o[r]))
+    want = ob.tonemap(lin_o[0] + lin_o[1], 2 * spp)  # f32 add in rank order, as the kernel does
+    got = rgb.cpu().numpy().reshape(h * w, 3)[band]
+    assert np.array_equal(got, want)
+    assert (parts[0][:, 3] == spp).all().item()

@@ -141,3 +141,92 @@ def test_walk_stats_instrumented_frame():
     b.scene.load_builtin(2)
     ws = b.walk_stats(2)
     assert ws.bvh_nodes == 0 and ws.node_visits == 0 and ws.leaf_tests == 0 and ws.rays > 0
+
+
+def test_config_d_fullsize_band_vs_accelerated_oracle():
+    """BASELINE config D as benched - 100 000 spheres + ground, 1920x1080, 64 spp, depth 50 - against the ORACLE (its
+    checker-side accelerator, pinned to its own scan by tests/test_oracle_bvh.py) on a two-row band: f32 sums and
+    RGB8 bytes bit for bit."""
+    d = generator().generate(100_000, seed=1234)
+    w, h, spp = 1920, 1080, 64
+    m = model(json.dumps(d), w, h, _lib.ACCEL_AUTO, 0)
+    rgb, lin = m.render(spp, want_linear=True)
+    assert m.stats().accel_in_use == _lib.ACCEL_LBVH and m.stats().bvh_nodes == 100_000 - 1
+    objs = so.flatten(d)
+    fr, at, up, fov = so.json_camera(d)
+    cam = ob.camera_look(fr, at, up, fov, w / h)
+    y0, y1 = 640, 642
+    rgb_o, lin_o, _ = ob.render(objs, cam, w, h, spp, seed=0, nthreads=os.cpu_count(), flags=ob.FLAG_BVH, y0=y0, y1=y1)
+    assert np.array_equal(bits(lin[y0:y1, :, :3]), bits(lin_o[y0:y1]))
+    assert np.array_equal(rgb[y0:y1], rgb_o[y0:y1])
+    assert len(np.unique(rgb[y0:y1].reshape(-1, 3), axis=0)) > 200  # the band looks at the sphere field
+
+
+def test_lbvh_negative_and_zero_radius_spheres():
+    """Sphere::hit only uses radius * radius (sphere.rs:27): r < 0 hits like |r| (the hollow-sphere idiom), r = 0 never
+    has disc > 0 but must not poison the walk's pad.  >= 16 primitives so that ACCEL_AUTO builds the tree."""
+    from test_oracle_analytic import sphere
+    rng = np.random.default_rng(11)
+    objs = []
+    for i in range(60):
+        c = rng.uniform(-6, 6, 3) + np.array([0, 0, -12.0])
+        r = float(rng.choice([-0.9, -0.4, 0.0, 0.5, 1.1]))
+        objs.append(sphere(tuple(c), r, mat=int(rng.integers(0, 4)), col=tuple(rng.uniform(0.2, 0.9, 3)), fuzz=0.1, id=i))
+    objs = np.stack(objs)
+    w, h = 256, 144
+    cam = ob.camera_look((0, 0, 3), (0, 0, -12), (0, 1, 0), 60.0, w / h)
+    out = []
+    for accel in (_lib.ACCEL_AUTO, _lib.ACCEL_BRUTE):
+        m = forma_b200.create_model(w, h, seed=9, accel=accel)
+        m.scene.load_objects(objs)
+        m.scene.camera.set_array(cam)
+        ids, t = m.primary_hits()
+        rgb, lin = m.render(3, want_linear=True)
+        out.append((ids, bits(t), bits(lin), rgb, m.stats().rays, m.stats().accel_in_use))
+    assert out[0][5] == _lib.ACCEL_LBVH and out[1][5] == _lib.ACCEL_BRUTE
+    for a, b in zip(out[0][:5], out[1][:5]):
+        assert np.array_equal(a, b)
+    ids_o, t_o = ob.primary_hits(objs, cam, w, h)
+    rgb_o, lin_o, rays_o = ob.render(objs, cam, w, h, 3, seed=9, nthreads=os.cpu_count())
+    assert np.array_equal(out[0][0], ids_o) and np.array_equal(out[0][1], bits(t_o))
+    assert out[0][4] == rays_o and np.array_equal(out[0][2][..., :3], bits(lin_o)) and np.array_equal(out[0][3], rgb_o)
+    assert (ids_o >= 0).mean() > 0.1
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_culls_and_pads_never_drop_a_hit(seed):
+    """Randomized differential test of scene_culled, beam_culled and the walk's pads (hand-derived rounding margins):
+    tiny spheres and thin triangles sitting at the corners of the scene's bounding box, cameras 1 to 100 scene radii
+    away, with and without the tree - against the oracle's plain scan, which has no cull at all."""
+    from test_oracle_analytic import sphere, tri
+    rng = np.random.default_rng(1000 + seed)
+    R = float(rng.choice([0.5, 5.0, 50.0]))
+    objs, k = [], 0
+    for sx in (-1, 1):
+        for sy in (-1, 1):
+            for sz in (-1, 1):
+                c = np.array([sx, sy, sz]) * R
+                if rng.random() < 0.5:
+                    objs.append(sphere(tuple(c), float(rng.choice([1e-3, 1e-2, 0.05])) * R, mat=int(rng.integers(0, 3)), id=k))
+                else:
+                    e = rng.uniform(-0.02, 0.02, (2, 3)) * R
+                    objs.append(tri(tuple(c), tuple(c + e[0]), tuple(c + e[1]), id=k))
+                k += 1
+    for _ in range(int(rng.choice([0, 12]))):  # with 12 more the scene has >= 16 primitives: the tree is built
+        objs.append(sphere(tuple(rng.uniform(-0.8, 0.8, 3) * R), float(rng.uniform(0.01, 0.2)) * R, mat=int(rng.integers(0, 3)), id=k))
+        k += 1
+    objs = np.stack(objs)
+    w, h = 96, 54
+    dist = float(rng.choice([1.0, 3.0, 30.0, 100.0])) * R * np.sqrt(3.0)
+    u = rng.normal(size=3); u /= np.linalg.norm(u)
+    at = rng.choice([-1.0, 1.0], 3) * R  # look at a corner
+    cam = ob.camera_look(tuple(at + u * dist), tuple(at), (0, 1, 0), float(rng.choice([10.0, 60.0])), w / h)
+    m = forma_b200.create_model(w, h, seed=seed, accel=_lib.ACCEL_AUTO)
+    m.scene.load_objects(objs)
+    m.scene.camera.set_array(cam)
+    ids, t = m.primary_hits()
+    rgb, lin = m.render(4, want_linear=True)
+    ids_o, t_o = ob.primary_hits(objs, cam, w, h)
+    rgb_o, lin_o, rays_o = ob.render(objs, cam, w, h, 4, seed=seed, nthreads=os.cpu_count())
+    assert np.array_equal(ids, ids_o) and np.array_equal(bits(t), bits(t_o))
+    assert m.stats().rays == rays_o and np.array_equal(bits(lin[..., :3]), bits(lin_o)) and np.array_equal(rgb, rgb_o)
