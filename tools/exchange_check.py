@@ -57,6 +57,7 @@ for f in range(frames):
             print(f"frame {f}: {int((host != want).any(-1).sum())} pixels differ", flush=True)
 torch.cuda.synchronize()
 dist.barrier()
+ex.close()  # unmap the peers' buffers (every rank is past its last frame: barrier above)
 if rank == 0:
     print(f"exchange_check: {frames} frames on {world} GPUs, {bad} bad", flush=True)
 # ---- the tile-interleaved split: rank 0's frame must equal ONE GPU's render of the same frame, bit for bit
@@ -84,6 +85,7 @@ for f in range(frames):
             print(f"tile frame {f}: {int((host != want).any(-1).sum())} pixels differ", flush=True)
 torch.cuda.synchronize()
 dist.barrier()
+tx.close()  # unmap, and give the handle its whole frame back
 if rank == 0:
     print(f"exchange_check (tiles): {frames} frames on {world} GPUs, {bad_t} bad", flush=True)
 bad += bad_t
