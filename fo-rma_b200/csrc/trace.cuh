@@ -29,7 +29,8 @@ __device__ __forceinline__ float length(float3 a) { return sqrtf(dot(a, a)); }
 __device__ __forceinline__ float3 unit(float3 a) { return a / length(a); }
 
 // ---- counter-based RNG (stands in for rand::thread_rng, utility.rs:5,16,33) -----------------------
-// Philox4x32-10 (Salmon et al., SC'11).  Key = seed; counter = (pixel, sample, slot, block).
+// Philox4x32-7 (Salmon et al., SC'11: the smallest Crush-resistant round count; the CPU checker draws from the
+// same generator with the same round count).  Key = seed; counter = (pixel, sample, slot, block).
 // slot 0 = camera draws of the path, slot 1+d = scatter at depth d.  f32 = (u32 >> 8) * 2^-24.
 struct Rand4 {
     float x, y, z, w;
@@ -37,10 +38,14 @@ struct Rand4 {
 // Round keys k + r*W are the same for every call of a launch, so the host expands them once
 // (RoundKeys, device_scene.hpp) and the kernel reads them as constant-bank operands: a round is
 // two IMAD.WIDE (hi and lo of each product in one instruction) and two 3-input LOP3.
-// the ten rounds: four u32 words
+#ifndef FORMA_PHILOX_ROUNDS
+#define FORMA_PHILOX_ROUNDS 7
+#endif
+constexpr int kPhiloxRounds = FORMA_PHILOX_ROUNDS;  // RoundKeys holds 10 rounds' keys; the first kPhiloxRounds are used
+// the rounds: four u32 words
 __device__ __forceinline__ uint4 philox_raw4(const RoundKeys& rk, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) {
 #pragma unroll
-    for (int r = 0; r < 10; ++r) {
+    for (int r = 0; r < kPhiloxRounds; ++r) {
         const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
         const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
         const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ rk.k[2 * r];

@@ -70,6 +70,8 @@ def lib():
                                     ctypes.c_void_p, ctypes.c_void_p]
         L.oracle_tonemap.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p]
         L.oracle_philox4x32_10.argtypes = [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
+        L.oracle_philox4x32_r.argtypes = [ctypes.c_int, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
+        L.oracle_path_rounds.restype = ctypes.c_int
         assert L.oracle_object_size() == OBJECT_DTYPE.itemsize
         assert L.oracle_camera_floats() == CAMERA_FLOATS
         _lib = L
@@ -90,11 +92,16 @@ def vec3_op(name, a, b):
     return np.array(out[:], dtype=np.float32)
 
 
-def philox(k0, k1, ctr):
+def philox(k0, k1, ctr, rounds=10):
     c = np.array(ctr, dtype=np.uint32)
     o = np.zeros(4, dtype=np.uint32)
-    lib().oracle_philox4x32_10(k0, k1, c.ctypes.data, o.ctypes.data)
+    lib().oracle_philox4x32_r(rounds, k0, k1, c.ctypes.data, o.ctypes.data)
     return o
+
+
+def path_rounds() -> int:
+    """Philox rounds of the path's counter RNG (oracle and kernels: 7)."""
+    return lib().oracle_path_rounds()
 
 
 def camera_new(w, h) -> np.ndarray:

@@ -23,7 +23,7 @@
 // RNG: the reference draws from rand::thread_rng() (third-party `rand` 0.8/0.9, ChaCha12, OS
 // seed; Cargo.lock:2724-2738).  Only its distribution can be matched: uniform f32 in [0,1) with
 // 24-bit resolution, (u32 >> 8) * 2^-24.  Two generators are offered:
-//   mode 0  counter-based Philox4x32-10 keyed (seed) with counter (pixel, sample, slot, block) —
+//   mode 0  counter-based Philox4x32-7 keyed (seed) with counter (pixel, sample, slot, block) —
 //           the generator the CUDA path uses, so same-RNG comparisons are meaningful;
 //   mode 1  a sequential per-thread xoshiro128++ stream consumed in the reference's order (Q14) —
 //           the stand-in for thread_rng in statistical (RMSE/PSNR) comparisons.
@@ -86,13 +86,18 @@ struct ReflectRecord {                                                // ray.rs:
 };
 
 // ----------------------------------------------------------------------------------------------
-// RNG (stand-in for rand::thread_rng; see header).  Philox4x32-10 is the published Random123
-// algorithm (Salmon et al., SC'11): 10 rounds, multipliers 0xD2511F53 / 0xCD9E8D57, Weyl key
-// increments 0x9E3779B9 / 0xBB67AE85.
+// RNG (stand-in for rand::thread_rng; see header).  Philox4x32-R is the published Random123
+// algorithm (Salmon et al., SC'11): R rounds, multipliers 0xD2511F53 / 0xCD9E8D57, Weyl key
+// increments 0x9E3779B9 / 0xBB67AE85.  The path draws from Philox4x32-7: the smallest round count the paper
+// reports as Crush-resistant (it passes BigCrush; 10 is Random123's default safety margin), pinned like the
+// 10-round form to Random123's published known-answer vectors (tests/test_oracle_analytic.py).  The choice of
+// generator is this build's, not the reference's (its thread_rng is OS-seeded ChaCha12): only the distribution of
+// the f32 draws is the reference's.  The CUDA kernels use the same round count (trace.cuh kPhiloxRounds).
 // ----------------------------------------------------------------------------------------------
-inline void philox4x32_10(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                          uint32_t out[4]) {
-    for (int r = 0; r < 10; ++r) {
+constexpr int kPathRounds = 7;
+inline void philox4x32(int rounds, uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                       uint32_t out[4]) {
+    for (int r = 0; r < rounds; ++r) {
         uint64_t p0 = (uint64_t)0xD2511F53u * c0;
         uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
         uint32_t hi0 = (uint32_t)(p0 >> 32), lo0 = (uint32_t)p0;
@@ -121,7 +126,7 @@ struct RngCtx {
 
     void block(uint32_t blk, float out[4]) const {
         uint32_t o[4];
-        philox4x32_10(k0, k1, pixel, sample, slot, blk, o);
+        philox4x32(kPathRounds, k0, k1, pixel, sample, slot, blk, o);
         for (int i = 0; i < 4; ++i) out[i] = u32_to_unit_f32(o[i]);
     }
     static uint32_t rotl(uint32_t x, int k) { return (x << k) | (x >> (32 - k)); }
@@ -727,8 +732,12 @@ void oracle_vec3_unit(const float* a, float* o) { Vec3 r = v3(a).unit_vector(); 
 
 // ---- RNG ----
 void oracle_philox4x32_10(uint32_t k0, uint32_t k1, const uint32_t* ctr, uint32_t* out) {
-    philox4x32_10(k0, k1, ctr[0], ctr[1], ctr[2], ctr[3], out);
+    philox4x32(10, k0, k1, ctr[0], ctr[1], ctr[2], ctr[3], out);
 }
+void oracle_philox4x32_r(int rounds, uint32_t k0, uint32_t k1, const uint32_t* ctr, uint32_t* out) {
+    philox4x32(rounds, k0, k1, ctr[0], ctr[1], ctr[2], ctr[3], out);
+}
+int oracle_path_rounds() { return kPathRounds; }
 float oracle_u32_to_f32(uint32_t v) { return u32_to_unit_f32(v); }
 
 // ---- optics helpers ----

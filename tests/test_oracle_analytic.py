@@ -41,6 +41,19 @@ def test_philox_kat(key, ctr, out):
     assert tuple(int(x) for x in ob.philox(key[0], key[1], ctr)) == out
 
 
+# ---- Philox4x32-7, the round count the path draws from: Random123's published known-answer vectors (kat_vectors,
+# "philox4x32 7 ...") for the same three inputs ------------------------------------------------------------------
+@pytest.mark.parametrize("key,ctr,out", [
+    ((0, 0), (0, 0, 0, 0), (0x5F6FB709, 0x0D893F64, 0x4F121F81, 0x4F730A48)),
+    ((0xFFFFFFFF, 0xFFFFFFFF), (0xFFFFFFFF,) * 4, (0x5207DDC2, 0x45165E59, 0x4D8EE751, 0x8C52F662)),
+    ((0xA4093822, 0x299F31D0), (0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344),
+     (0x4DFCCABA, 0x190A87F0, 0xC47362BA, 0xB6B5242A)),
+])
+def test_philox7_kat(key, ctr, out):
+    assert ob.path_rounds() == 7
+    assert tuple(int(x) for x in ob.philox(key[0], key[1], ctr, rounds=7)) == out
+
+
 def test_unit_float_is_rand_standard_f32():
     # rand's Standard f32: (u32 >> 8) * 2^-24, in [0, 1)
     L = ob.lib()
