@@ -200,7 +200,9 @@ constexpr int kBatchSamples = FORMA_BATCH_SAMPLES;
 // moment its path ends, so every lane of every warp traces one ray per iteration until the queue is empty.  A finished
 // path stores its radiance in rad[sample][pixel]; accumulate_kernel adds them per pixel in sample order (the f32
 // chain of tracer.rs:170-175: bit-identical sums).  600x600x50 spp: get_simple_scene 5.49 -> 1.17 ms, get_objects
-// 5.45 -> 1.31 ms.
+// 5.45 -> 1.31 ms.  Measured and dropped (profiles/r05m_perf.txt): a per-lane state machine that runs the Philox
+// blocks of camera rays, scatter tries and rejection retries in common passes (1-3 per round) ahead of one trace pass -
+// bit-exact, but 80 registers and a thinner trace pass: 21.4 ms against this loop's 18.4 ms at 1080p x 64 spp.
 #ifndef FORMA_QUEUE_MIN_BLOCKS
 #define FORMA_QUEUE_MIN_BLOCKS 6
 #endif
@@ -844,13 +846,14 @@ cudaError_t launch_render(const RenderParams& P, int sm_count, cudaStream_t stre
         return launch_queue_chunks(render_tree_kernel<false>, 0, P, sm_count, stream, launches);
     }
     if (P.queue) {
+        const auto k_smem = render_queue_kernel<kScanSmem>;
+        const auto k_glob = render_queue_kernel<kScanGlobal>;
         if (P.scene.smem_bytes > 0) {
-            cudaError_t e = cudaFuncSetAttribute(render_queue_kernel<kScanSmem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 P.scene.smem_bytes);
+            cudaError_t e = cudaFuncSetAttribute(k_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, P.scene.smem_bytes);
             if (e != cudaSuccess) return e;
-            return launch_queue_chunks(render_queue_kernel<kScanSmem>, (size_t)P.scene.smem_bytes, P, sm_count, stream, launches);
+            return launch_queue_chunks(k_smem, (size_t)P.scene.smem_bytes, P, sm_count, stream, launches);
         }
-        return launch_queue_chunks(render_queue_kernel<kScanGlobal>, 0, P, sm_count, stream, launches);
+        return launch_queue_chunks(k_glob, 0, P, sm_count, stream, launches);
     }
     const dim3 grid = tile_grid(P.width, P.height);
     if (P.scene.smem_bytes > 0) {

@@ -462,6 +462,9 @@ constexpr int kWalkPop = (int)0x80000001;   // convergent walk: this lane takes 
 #ifndef FORMA_SMEM_STACK
 #define FORMA_SMEM_STACK 8
 #endif
+#ifndef FORMA_WALK_PREFETCH
+#define FORMA_WALK_PREFETCH 0
+#endif
 constexpr int kSmemStack = FORMA_SMEM_STACK, kStackCap = 64, kWalkBlock = 128;
 struct WalkStack {
     uint32_t sbase;  // shared-window byte address of level 0 of this thread; level l at sbase + l * 8 * kWalkBlock
@@ -517,6 +520,11 @@ __device__ __forceinline__ void walk_inner(const SceneView& S, const RayGrid& g,
     stack.push_if(both, sp, other, fmaxf(nearL, nearR));
     sp += both ? 1 : 0;
     node = (hitL || hitR) ? enter : kWalkPop;
+#if FORMA_WALK_PREFETCH
+    // the child this lane enters is known ~30 instructions (vote, loop, pop logic) before its record is loaded:
+    // start the L2 -> L1 transfer now
+    if (node >= 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(S.bvh_nodes + 2 * (size_t)node));
+#endif
 }
 
 // MODE selects what a kernel instantiation carries: the brute-force scan with the primitives staged
@@ -555,49 +563,62 @@ __device__ __forceinline__ void closest_hit(const SceneView& S, const float4* __
 }
 
 // ---- scatter (sphere.rs:53-152, plane.rs:46-122) ----------------------------------------------------
-// Returns false when the path is absorbed (metal, sphere.rs:104).  `slot` = 1 + depth.
-__device__ __forceinline__ bool scatter(const SceneView& S, const PathRng& rng, uint32_t slot, float3 d,
-                                        const HitState& h, float3& new_o, float3& new_d) {
-    const int km = S.kindmat[h.obj];
+// The part of scatter that follows the random draws: `rs` = the accepted random_in_unit_sphere sample (unused by the
+// dielectric), `rw` = get_random() (lane w of block 0; used by the dielectric only).  Returns false when the path is
+// absorbed (metal, sphere.rs:104).
+__device__ __forceinline__ bool scatter_finish(const SceneView& S, float3 d, float3 hp, float3 hn, int hobj, float3 rs,
+                                               float rw, float3& new_o, float3& new_d) {
+    const int km = S.kindmat[hobj];
     const int kind = km & 0xff, material = km >> 8;
-    const Rand4 r = rng.block(slot, 0);
-    new_o = h.p;
+    new_o = hp;
     const bool dielectric = material == 2 && kind == FORMA_RT_SPHERE;
-    // metal (sphere.rs:97, also at fuzz 0: Q7), lambertian and "light" all draw random_in_unit_sphere: ONE rejection
-    // loop for the lanes of all three, instead of one per material branch
-    float3 rs = f3(0.0f, 0.0f, 0.0f);
-    if (!dielectric) rs = random_in_unit_sphere(rng, slot, r);
     if (material == 1) {  // metal: sphere.rs:91-105 == plane.rs:108-122
-        float fuzz = S.material[h.obj].w;
-        float3 reflected = reflect(unit(d), h.n);
+        float fuzz = S.material[hobj].w;
+        float3 reflected = reflect(unit(d), hn);
         new_d = reflected + fuzz * rs;
-        return dot(new_d, h.n) > 0.0f;
+        return dot(new_d, hn) > 0.0f;
     }
     if (dielectric) {  // sphere.rs:107-145 (spheres only, plane.rs:52-59)
         const float ref_idx = 1.3f;
         float3 outward_normal = f3(0.0f, 0.0f, 0.0f);
-        float3 reflected = reflect(d, h.n);
+        float3 reflected = reflect(d, hn);
         float ni_over_nt, cosine, reflect_prob;
         float3 refracted = f3(0.0f, 0.0f, 0.0f);
-        float dn = dot(d, h.n);
+        float dn = dot(d, hn);
         if (dn > 0.0f) {
-            outward_normal = outward_normal - h.n;
+            outward_normal = outward_normal - hn;
             ni_over_nt = ref_idx;
             cosine = ref_idx * dn / length(d);
         } else {
-            outward_normal = h.n;
+            outward_normal = hn;
             ni_over_nt = 1.0f / ref_idx;
             cosine = -dn / length(d);
         }
         if (refract(d, outward_normal, ni_over_nt, refracted)) reflect_prob = schlick(cosine, ref_idx);
         else reflect_prob = 1.0f;
-        new_d = (r.w < reflect_prob) ? reflected : refracted;  // get_random(): lane w of block 0
+        new_d = (rw < reflect_prob) ? reflected : refracted;  // get_random(): lane w of block 0
         return true;
     }
     // lambertian (sphere.rs:84-89, plane.rs:101-106) and "light" (sphere.rs:147-152): same ray
-    float3 target = h.p + h.n + rs;
-    new_d = target - h.p;
+    float3 target = hp + hn + rs;
+    new_d = target - hp;
     return true;
+}
+// true: list entry `obj` scatters as a dielectric (one get_random() draw, no unit-sphere sample)
+__device__ __forceinline__ bool is_dielectric(const SceneView& S, int obj) {
+    const int km = S.kindmat[obj];
+    return (km >> 8) == 2 && (km & 0xff) == FORMA_RT_SPHERE;
+}
+
+// Returns false when the path is absorbed (metal, sphere.rs:104).  `slot` = 1 + depth.
+__device__ __forceinline__ bool scatter(const SceneView& S, const PathRng& rng, uint32_t slot, float3 d,
+                                        const HitState& h, float3& new_o, float3& new_d) {
+    const Rand4 r = rng.block(slot, 0);
+    // metal (sphere.rs:97, also at fuzz 0: Q7), lambertian and "light" all draw random_in_unit_sphere: ONE rejection
+    // loop for the lanes of all three, instead of one per material branch
+    float3 rs = f3(0.0f, 0.0f, 0.0f);
+    if (!is_dielectric(S, h.obj)) rs = random_in_unit_sphere(rng, slot, r);
+    return scatter_finish(S, d, h.p, h.n, h.obj, rs, r.w, new_o, new_d);
 }
 
 // attenuation of list entry `obj` (sphere.rs:87,101,116,150): colour, or one for a sphere "light"
