@@ -168,24 +168,12 @@ void quat(const Value& o, const char* key, const char* ctx, float q[4]) {
 }  // namespace
 
 void load_json_scene(const char* text, size_t len, std::vector<forma_rt_object>& objects, JsonCamera& cam) {
-    Value root = json::parse(text, len);
-    if (root.type != Value::Object) throw std::runtime_error("scene JSON: top level is not an object");
-    // SceneData { camera, lights, objects } — all three are required by serde (scene_loader.rs:10-14)
-    const Value& jcam = need(root, "camera", Value::Object, "scene");
-    need(root, "lights", Value::Array, "scene");
-    const Value& jobjs = need(root, "objects", Value::Array, "scene");
-
-    JsonCamera c;
-    c.present = true;
-    c.position = vec3(jcam, "position", "camera");
-    quat(jcam, "rotation", "camera", c.rotation);
-    c.fov = num(jcam, "fov", "camera");
-
     std::vector<forma_rt_object> out;
     size_t oi = 0;
-    for (const Value& jo : jobjs.arr) {
+    // objects[] entries are mapped as they are parsed (json.hpp parse_streaming): no DOM of the whole array
+    auto on_object = [&](Value&& jo) {
         if (jo.type != Value::Object) throw std::runtime_error("scene JSON: objects[] entry is not an object");
-        const std::string& mesh = need(jo, "mesh", Value::String, "object").str;
+        const std::string& mesh = need(jo, "mesh", Value::String, "object").str();
         need(jo, "material", Value::String, "object");  // rasteriser material name: required, not used here
         V3 position = vec3(jo, "position", "object");
         float rot[4];
@@ -198,12 +186,12 @@ void load_json_scene(const char* text, size_t len, std::vector<forma_rt_object>&
         proto.color[0] = 0.263f; proto.color[1] = 0.208f; proto.color[2] = 0.655f;
         if (const Value* rt = jo.find("rt"); rt && rt->type == Value::Object) {
             if (const Value* m = rt->find("material"); m && m->type == Value::String) {
-                if (m->str == "metal") proto.material = 1;
-                else if (m->str == "dielectric") proto.material = 2;
-                else if (m->str == "light") proto.material = 3;
+                if (m->str() == "metal") proto.material = 1;
+                else if (m->str() == "dielectric") proto.material = 2;
+                else if (m->str() == "light") proto.material = 3;
             }
-            if (const Value* col = rt->find("color"); col && col->type == Value::Array && col->arr.size() == 3)
-                for (int k = 0; k < 3; ++k) proto.color[k] = (float)col->arr[k].num;
+            if (const Value* col = rt->find("color"); col && col->type == Value::Array && col->arr().size() == 3)
+                for (int k = 0; k < 3; ++k) proto.color[k] = (float)col->arr()[k].num;
             if (const Value* f = rt->find("fuzz"); f && f->type == Value::Number) proto.fuzz = (float)f->num;
         }
         // ids pack the object index into the upper 16 bits; past 65535 objects it wraps (mod 2^16)
@@ -240,7 +228,20 @@ void load_json_scene(const char* text, size_t len, std::vector<forma_rt_object>&
             }
         }
         ++oi;
-    }
+    };
+    Value root = json::Parser(text, len).parse_streaming("objects", on_object);
+    if (root.type != Value::Object) throw std::runtime_error("scene JSON: top level is not an object");
+    // SceneData { camera, lights, objects } — all three are required by serde (scene_loader.rs:10-14)
+    const Value& jcam = need(root, "camera", Value::Object, "scene");
+    need(root, "lights", Value::Array, "scene");
+    need(root, "objects", Value::Array, "scene");
+
+    JsonCamera c;
+    c.present = true;
+    c.position = vec3(jcam, "position", "camera");
+    quat(jcam, "rotation", "camera", c.rotation);
+    c.fov = num(jcam, "fov", "camera");
+
     objects.swap(out);
     cam = c;
 }
