@@ -569,6 +569,31 @@ def multi_gpu_configs(rig, m_c, ex_c, d_rgb_c, steps):
         record("C strong: scene_09 1080p, 256 spp TOTAL, sample-split", "strong", ms_n, ms_1, rays, m_c, parity,
                f"{spr} spp per GPU; fused peer-memory reduce + tone-map, flag-ordered")
 
+    # ---- C strong, tile-interleaved: the same 256-spp frame with the OTHER partition north_star names - every rank traces
+    # all samples of its own 32x4 tiles and stores RGB8 into rank 0's frame; no reduce, bit-exact against one GPU
+    m = forma_b200.create_model(W, H, device=rig.local, seed=SEED)
+    m.scene.load_json(open(SCENE).read()); m.scene.camera.use_json()
+    tx = make_exchange(rig, m, "tile")
+    if tx:
+        for _ in range(3):
+            tx.frame(SPP, DEPTH, rig.stream)
+        ms_n, _ = rig.time_steps(lambda: tx.frame(SPP, DEPTH, rig.stream), steps)
+        rays = rig.sum_over_ranks(m.stats().rays)
+        parity = None
+        if rank == 0:
+            rig.ts.synchronize()
+            got = frame_bytes(tx.rgb0, W * H * 3)
+            m_c.render_device(SPP, 0, DEPTH, d_rgb_c.data_ptr(), None, rig.stream)
+            rig.ts.synchronize()
+            parity = "ok" if np.array_equal(got, d_rgb_c.cpu().numpy()) else "bad"
+        rig.sync()
+        ms_1 = solo(lambda: m_c.render_device(SPP, 0, DEPTH, d_rgb_c.data_ptr(), None, rig.stream))
+        record("C strong: scene_09 1080p, 256 spp TOTAL, tile-interleaved", "strong", ms_n, ms_1, rays, m, parity,
+               "every rank traces all 256 samples of its 32x4 tiles and stores RGB8 into rank 0's frame over NVLink; no reduce")
+        rig.sync()
+        tx.close()
+    m.close()
+
     # ---- E: scene_09 at 3840x2160, 512 spp per GPU, sample-split (N = 8 is BASELINE.json's 4096-spp config E)
     w, h, spp = 3840, 2160, 512
     m = forma_b200.create_model(w, h, device=rig.local, seed=SEED)
