@@ -1201,6 +1201,10 @@ extern "C" int forma_rt_render_device_noalloc(forma_rt* ctx, uint32_t spp, uint3
     CU_TRY(cudaEventRecord(ctx->ev_k0, s));
     CU_TRY(forma::launch_render_noalloc(P, ctx->device, ctx->sm_count, s, &launches));
     CU_TRY(cudaEventRecord(ctx->ev_k1, s));
+    if (d_rgb && (ctx->flags & FORMA_RT_SRGB_OUT)) {  // as forma_rt_render_device: the table travels as a kernel parameter
+        CU_TRY(forma::launch_srgb_encode((uint8_t*)d_rgb, (size_t)npix * 3, ctx->srgb_lut, ctx->sm_count, s));
+        ++launches;
+    }
     ctx->stats.gpu_launches = launches;
     ctx->stats.paths = npix * spp;  // under forma_rt_set_partition: an upper bound (the handle's own tiles only are traced)
     ctx->stats_pending = true;

@@ -6,6 +6,7 @@
 // Built with -fmad=false (see trace.cuh).
 #include <algorithm>
 #include <cstdio>
+#include <mutex>
 
 #include "kernels.hpp"
 #include "trace.cuh"
@@ -35,7 +36,7 @@ __device__ __forceinline__ void stage_scene(const SceneView& S, const float4*& s
 // tracer.rs:177-184 for one pixel per thread: f32 sum out, and / or average in linear space, sqrt
 // gamma, (c * 255.0) as u8 — the RGB8 tile staged in shared memory and stored as coalesced words.
 __device__ __forceinline__ void write_out(const RenderParams& P, float3 col, uint32_t x, uint32_t y, int lx, int ly,
-                                          bool live, uint8_t (*tile_rgb)[kTileW * 3]) {
+                                          bool live, uint8_t (*tile_rgb)[kTileW * 3], uint32_t bx, uint32_t by) {
     const float n_spp = (float)(P.spp + P.spp_prior);
     if (P.sum && live) P.sum[(size_t)x + (size_t)y * P.width] = make_float4(col.x, col.y, col.z, n_spp);
 
@@ -44,7 +45,7 @@ __device__ __forceinline__ void write_out(const RenderParams& P, float3 col, uin
         float3 c = col / n_spp;
         const uint32_t r = as_u8(sqrtf(c.x) * 255.0f), g = as_u8(sqrtf(c.y) * 255.0f), b = as_u8(sqrtf(c.z) * 255.0f);
         // word stores need a 4-byte aligned frame (a caller's device pointer may be a slice) and rows that are whole words
-        const bool full_tile = (blockIdx.x + 1) * kTileW <= P.width && (blockIdx.y + 1) * kTileH <= P.height &&
+        const bool full_tile = (bx + 1) * kTileW <= P.width && (by + 1) * kTileH <= P.height &&
                                (P.width * 3u) % 4u == 0 && (reinterpret_cast<uintptr_t>(P.rgb) & 3u) == 0u;
         if (full_tile) {  // stage 4 rows x 96 bytes, write them as 96 coalesced 32-bit words
             tile_rgb[ly][lx * 3 + 0] = (uint8_t)r;
@@ -53,7 +54,7 @@ __device__ __forceinline__ void write_out(const RenderParams& P, float3 col, uin
             __syncthreads();
             if (threadIdx.x < kTileH * 24) {
                 const int row = threadIdx.x / 24, word = threadIdx.x % 24;
-                const size_t byte = ((size_t)(blockIdx.y * kTileH + row) * P.width + (size_t)blockIdx.x * kTileW) * 3;
+                const size_t byte = ((size_t)(by * kTileH + row) * P.width + (size_t)bx * kTileW) * 3;
                 reinterpret_cast<uint32_t*>(P.rgb + byte)[word] = reinterpret_cast<const uint32_t*>(tile_rgb[row])[word];
             }
         } else if (live) {
@@ -68,7 +69,12 @@ __device__ __forceinline__ void write_out(const RenderParams& P, float3 col, uin
 #endif
 template <int MODE>
 __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(const __grid_constant__ RenderParams P) {
-    if ((blockIdx.y * P.part_pitch + blockIdx.x) % P.part_mod != P.part_rem) return;  // another GPU's tile
+    // The grid is 1-D over the tiles THIS launch owns: CTA j traces tile t = j * part_mod + part_rem of a part_pitch-wide
+    // tile grid (forma_rt_set_partition; one GPU: t = j).  Launching every tile and letting the other GPUs' CTAs return
+    // starved the SMs of working CTAs: config C split 8 ways took 1.63 ms per rank instead of 0.5 (profiles/r05v).
+    const uint32_t t = blockIdx.x * P.part_mod + P.part_rem;
+    const uint32_t bx = t % P.part_pitch, by = t / P.part_pitch;
+    if (bx * kTileW >= P.width) return;  // a padding column of the pitch (uniform for the CTA)
     const float4 *sph, *tri;
     stage_scene<MODE>(P.scene, sph, tri);
 
@@ -76,7 +82,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int lx = warp * 8 + (lane & 7), ly = lane >> 3;
-    const uint32_t x = blockIdx.x * kTileW + lx, y = blockIdx.y * kTileH + ly;
+    const uint32_t x = bx * kTileW + lx, y = by * kTileH + ly;
     const bool live = x < P.width && y < P.height;
 
     uint32_t rays = 0, culled = 0;
@@ -180,7 +186,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_SCAN_MIN_BLOCKS) render_kernel(c
     wr = __reduce_add_sync(0xffffffffu, culled);
     if (lane == 0 && wr) atomicAdd(P.rays + 1, (unsigned long long)wr);
 
-    write_out(P, col, x, y, lx, ly, live, tile_rgb);
+    write_out(P, col, x, y, lx, ly, live, tile_rgb, bx, by);
 }
 
 // A batch is what a warp holds when the queue runs dry, i.e. the drain at the end of a launch: at 8 samples (256
@@ -855,7 +861,10 @@ cudaError_t launch_render(const RenderParams& P, int sm_count, cudaStream_t stre
         }
         return launch_queue_chunks(k_glob, 0, P, sm_count, stream, launches);
     }
-    const dim3 grid = tile_grid(P.width, P.height);
+    // the tiles this launch owns: t = j * part_mod + part_rem < part_pitch * tile rows
+    const uint32_t n_tiles = P.part_pitch * ((P.height + kTileH - 1) / kTileH);
+    const dim3 grid(n_tiles > P.part_rem ? (n_tiles - P.part_rem + P.part_mod - 1) / P.part_mod : 0u);
+    if (grid.x == 0) return cudaSuccess;
     if (P.scene.smem_bytes > 0) {
         cudaError_t e = cudaFuncSetAttribute(render_kernel<kScanSmem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              P.scene.smem_bytes);
@@ -986,7 +995,10 @@ __global__ void flag_wait_kernel(const __grid_constant__ FlagPtrs p, int n, uint
             if ((int32_t)(x - value) >= 0) break;
             if ((spin & 1023u) == 1023u) {
                 asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-                if (t1 - t0 > timeout_ns) { if (err) atomicCAS(err, 0u, 1u + threadIdx.x); break; }
+                if (t1 - t0 > timeout_ns) {  // plain stores: the word is host-mapped, no atomics needed to report ONE late flag
+                    if (err && *(volatile unsigned int*)err == 0u) *(volatile unsigned int*)err = 1u + threadIdx.x;
+                    break;
+                }
             }
         }
     }
@@ -1028,12 +1040,16 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
 cudaError_t launch_render_noalloc(RenderParams P, int device, int sm_count, cudaStream_t stream, uint32_t* launches) {
     *launches = 0;
     static void* base_of_device[64] = {};
+    static std::mutex base_lock;  // handles of several host threads may meet here for the first time
     if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
-    if (!base_of_device[device]) {  // set-up, once per device; the caller has made `device` current
-        void* p = nullptr;
-        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
-        if (e != cudaSuccess) return e;
-        base_of_device[device] = p;
+    {
+        std::lock_guard<std::mutex> guard(base_lock);
+        if (!base_of_device[device]) {  // set-up, once per device; the caller has made `device` current
+            void* p = nullptr;
+            const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess) return e;
+            base_of_device[device] = p;
+        }
     }
     const size_t npix = (size_t)P.width * P.height;
     if (npix == 0 || npix > kNoAllocSlots) return cudaErrorInvalidValue;  // the entry point reports this with the limit

@@ -82,3 +82,11 @@ def test_noalloc_rejects_what_it_cannot_do():
     with pytest.raises(_lib.FormaError):
         m.render_device_noalloc(1, 0, 50, 1, None)
     m.close()
+
+
+def test_noalloc_honours_the_srgb_output_flag():
+    m = forma_b200.create_model(160, 96, device=0, seed=5, flags=_lib.SRGB_OUT)
+    m.scene.load_builtin(0)
+    m.scene.camera.orbit((0.0, 0.0, 0.0))
+    check_pair(m, 4)
+    m.close()
