@@ -603,13 +603,15 @@ int flag_timed_out(forma_rt* c) {
                 " ms (a peer rank died, or two ranks share one GPU); the frame is incomplete");
 }
 
-// Scan mode has two kernels (kernels.cu): a pixel per thread (render_kernel: unbeatable while a frame is mostly sky -
-// config C runs its camera-ray -> sky loop - and for a 1-spp frame, where a queue has nothing to refill lanes with)
-// and (pixel, sample) jobs from a queue (render_queue_kernel: balanced whatever the per-pixel cost).  The queue is
-// used for multi-sample frames that can bounce: planes or non-finite geometry (the beam cull of render_kernel never
-// applies), or the scene's bounding sphere covers more than a fifth of a coarse grid of primary rays (f64, same
-// geometry as beam_culled: distance of the central ray to the sphere's centre).  FORMA_RT_SCAN_QUEUE=0 / 1 overrides
-// (A/B measurements).
+// Scan mode has two kernels (kernels.cu): a pixel per thread (render_kernel) and (pixel, sample) jobs from a queue
+// (render_queue_kernel).  The pixel loop has the least overhead per path - no radiance buffer, no job logic, the
+// beam-culled sky loop - and wins wherever paths are short and alike: config C, a 1-spp frame (a queue has nothing to
+// refill a lane with), and an object seen from OUTSIDE at any coverage (tools/coverage_probe.py: scene_09's tetrahedron
+// filling 0.1 % .. 63 % of a 1080p frame, 1.08 .. 5.7 ms against the queue's 2.5 .. 8.3 ms).  The queue wins when paths
+// get trapped and per-pixel cost varies wildly - the eye INSIDE the geometry, a ground sphere or a plane under
+// everything, as in every scene of scenes.rs: 600x600x50 spp 5.45 -> 1.08 ms, 1080p x 64 spp 23.5 -> 18.4 ms.  So: the
+// queue for >= 4 spp when the scene has planes or non-finite geometry (never culled, order-sensitive), or when the
+// eye lies inside the bounding sphere of the spheres and triangles.  FORMA_RT_SCAN_QUEUE=0 / 1 overrides (A/B runs).
 bool frame_bounces(const forma_rt* c, uint32_t spp) {
     if (const char* e = std::getenv("FORMA_RT_SCAN_QUEUE")) return std::atoi(e) != 0;
     if (spp < 4) return false;
@@ -617,22 +619,12 @@ bool frame_bounces(const forma_rt* c, uint32_t spp) {
     if (v.n_spheres + v.n_tris + v.n_planes == 0) return false;
     if (v.n_planes != 0 || !(v.cull_r2 < FLT_MAX)) return true;
     const forma_rt_camera& k = c->scene.camera.c;
-    const double R = std::sqrt((double)v.cull_r2) * 1.05;
-    int hit = 0, n = 0;
-    for (int gy = 0; gy < 27; ++gy)
-        for (int gx = 0; gx < 48; ++gx, ++n) {
-            const double s = (gx + 0.5) / 48.0, t = (gy + 0.5) / 27.0;
-            double D[3], m[3], dd = 0.0, md = 0.0, mm = 0.0;
-            for (int i = 0; i < 3; ++i) {
-                D[i] = (double)k.lower_left_corner[i] + s * (double)k.horizontal[i] + t * (double)k.vertical[i] - (double)k.position[i];
-                m[i] = (double)k.position[i] - (double)v.cull_center[i];
-                dd += D[i] * D[i]; md += m[i] * D[i]; mm += m[i] * m[i];
-            }
-            // closest approach of pos + tau D, tau >= 0, to the centre
-            const double d2 = (md < 0.0 && dd > 0.0) ? mm - md * md / dd : mm;
-            hit += !(d2 > R * R);  // NaN counts as a hit
-        }
-    return hit * 5 > n;
+    double mm = 0.0;
+    for (int i = 0; i < 3; ++i) {
+        const double m = (double)k.position[i] - (double)v.cull_center[i];
+        mm += m * m;
+    }
+    return !(mm > (double)v.cull_r2);  // NaN counts as inside
 }
 
 // One launch of the trace kernel on `stream`; outputs are device pointers.  Records kernel events.
