@@ -58,7 +58,10 @@ struct DevBuf {
 };
 
 constexpr int kSmemStageLimit = 96 * 1024;   // stage spheres+tris in shared memory up to this size
-constexpr uint32_t kBvhThreshold = 16;       // ACCEL_AUTO: LBVH at or above this many spheres + triangles
+// ACCEL_AUTO: LBVH when spheres + 2 x triangles reaches this (a triangle costs about two spheres to scan).  Swept on
+// the sphere-field generator at 1080p (tools/accel_threshold_probe.py, profiles/r05z_accel_threshold.txt): 16 spheres scan 2.58 ms
+// / tree 3.20 ms, 24: 3.00 / 3.26, 32: 3.42 / 3.40, 64: 5.15 / 3.72.  Round 1's value was 16 primitives, unswept.
+constexpr uint32_t kBvhThreshold = 32;
 constexpr size_t kRadBudget = 4ull << 30;    // tree mode: bytes of per-path radiance kept between trace and accumulate
                                              // (64 samples of a 1080p frame = 2.1 GB in ONE launch: every launch ends with a drain)
 
@@ -204,7 +207,7 @@ int upload_scene(forma_rt* c) {
     // The tree needs every sphere/triangle in ONE run of the list (planes may precede or follow it).
     int runs = 0;
     for (const Segment& g : segments) runs += (g.sph_end > g.sph_begin || g.tri_end > g.tri_begin) ? 1 : 0;
-    const bool want_bvh = c->accel == FORMA_RT_ACCEL_LBVH || (c->accel == FORMA_RT_ACCEL_AUTO && ns + nt >= kBvhThreshold);
+    const bool want_bvh = c->accel == FORMA_RT_ACCEL_LBVH || (c->accel == FORMA_RT_ACCEL_AUTO && ns + 2 * nt >= kBvhThreshold);
     if (c->accel == FORMA_RT_ACCEL_LBVH && runs > 1)
         return fail(FORMA_RT_EINVAL, "LBVH needs all spheres and triangles in one plane-free run of Scene.objects; use FORMA_RT_ACCEL_BRUTE");
     LbvhInput bin{};

@@ -46,7 +46,7 @@ extern "C" {
 #define FORMA_RT_SRGB_OUT 8u  /* RGB8 outputs pass through color_utils::srgb_encode (color_utils.rs:49-66) on the GPU (added mode) */
 
 /* forma_rt_options.accel */
-#define FORMA_RT_ACCEL_AUTO 0u  /* brute-force scan below FORMA_RT_BVH_THRESHOLD spheres, LBVH above */
+#define FORMA_RT_ACCEL_AUTO 0u  /* brute-force scan for small scenes, LBVH once spheres + 2 x triangles >= 32 (the measured crossover) */
 #define FORMA_RT_ACCEL_BRUTE 1u /* tracer.rs:195-200's linear scan, as-is */
 #define FORMA_RT_ACCEL_LBVH 2u  /* on-GPU Morton-code LBVH over the spheres (reference has none: aabb.rs is a stub) */
 

@@ -164,7 +164,7 @@ def test_config_d_fullsize_band_vs_accelerated_oracle():
 
 def test_lbvh_negative_and_zero_radius_spheres():
     """Sphere::hit only uses radius * radius (sphere.rs:27): r < 0 hits like |r| (the hollow-sphere idiom), r = 0 never
-    has disc > 0 but must not poison the walk's pad.  >= 16 primitives so that ACCEL_AUTO builds the tree."""
+    has disc > 0 but must not poison the walk's pad.  60 spheres: ACCEL_AUTO builds the tree (spheres + 2 x triangles >= 32)."""
     from test_oracle_analytic import sphere
     rng = np.random.default_rng(11)
     objs = []
@@ -212,7 +212,7 @@ def test_culls_and_pads_never_drop_a_hit(seed):
                     e = rng.uniform(-0.02, 0.02, (2, 3)) * R
                     objs.append(tri(tuple(c), tuple(c + e[0]), tuple(c + e[1]), id=k))
                 k += 1
-    for _ in range(int(rng.choice([0, 12]))):  # with 12 more the scene has >= 16 primitives: the tree is built
+    for _ in range(int(rng.choice([0, 30]))):  # with 30 more spheres ACCEL_AUTO builds the tree (spheres + 2 x triangles >= 32)
         objs.append(sphere(tuple(rng.uniform(-0.8, 0.8, 3) * R), float(rng.uniform(0.01, 0.2)) * R, mat=int(rng.integers(0, 3)), id=k))
         k += 1
     objs = np.stack(objs)
