@@ -317,3 +317,21 @@ def test_edge_cases_empty_tiny_and_degenerate():
         assert np.array_equal(ids, ids_o) and np.array_equal(bits(t), bits(t_o))
         assert 0 in ids and 1 not in ids and 2 not in ids and 13 not in ids
     assert m.stats().accel_in_use == _lib.ACCEL_LBVH
+
+
+@pytest.mark.parametrize("w,h", [(67, 45), (33, 5), (130, 7), (5, 3), (1, 1), (3, 64)])
+def test_job_queue_paths_on_ragged_frames(w, h):
+    """accumulate_kernel owns groups of four pixels of a row and stores whole groups as three 32-bit words: widths
+    that are not multiples of 4 (byte path, short last group), frames smaller than a tile, one pixel - through
+    render_queue_kernel (get_objects, 5 spp: the eye is inside the ground sphere's bounds) and through
+    render_tree_kernel (scene_01 with the LBVH forced, 4 spp), bit-exact against the oracle."""
+    m = forma_b200.create_model(w, h, seed=77)
+    m.scene.load_builtin(2)
+    assert_render_equal(m, ob.builtin_scene(2), ob.camera_new(w, h), w, h, 5, 77)
+    assert m.stats().gpu_launches == 2  # trace + accumulate: the job-queue scan, not the pixel kernel
+    txt, objs, cam = load_scene_pair("scene_01", w, h)
+    m = forma_b200.create_model(w, h, seed=78, accel=_lib.ACCEL_LBVH)
+    m.scene.load_json(txt)
+    m.scene.camera.use_json()
+    assert_render_equal(m, objs, cam, w, h, 4, 78)
+    assert m.stats().accel_in_use == _lib.ACCEL_LBVH
