@@ -212,7 +212,7 @@ int upload_scene(forma_rt* c) {
         return fail(FORMA_RT_EINVAL, "LBVH needs all spheres and triangles in one plane-free run of Scene.objects; use FORMA_RT_ACCEL_BRUTE");
     LbvhInput bin{};
     bool use_bvh = false;
-    float bc[3] = {0, 0, 0}, br2 = 0.0f, beps = 0.0f, qstep[3] = {0, 0, 0}, bq = 0.0f;
+    float bc[3] = {0, 0, 0}, br2 = 0.0f, beps = 0.0f, qstep[3] = {0, 0, 0}, bq = 0.0f, brmax = 0.0f;
     if (want_bvh && runs == 1 && ns + nt >= 2) {
         const int NS = (int)ns, NT = (int)nt, N = NS + NT;
         std::vector<V3> lo(N), hi(N);
@@ -311,7 +311,7 @@ int upload_scene(forma_rt* c) {
                 bin.qinv[k] = 1.0f / qstep[k];
             }
             bq = 0.0f;  // max 1/|r| over the spheres of the tree (the outsized ones were moved to the front)
-            for (int i = big_s; i < NS; ++i) bq = std::max(bq, 1.0f / std::fabs(spheres[i].w));
+            for (int i = big_s; i < NS; ++i) { bq = std::max(bq, 1.0f / std::fabs(spheres[i].w)); brmax = std::max(brmax, std::fabs(spheres[i].w)); }
             use_bvh = true;
         }
     }
@@ -374,7 +374,7 @@ int upload_scene(forma_rt* c) {
         for (size_t k = 0; k < segments.size(); ++k)
             if (segments[k].sph_end > segments[k].sph_begin || segments[k].tri_end > segments[k].tri_begin) v.tree_seg = (int)k;
         v.bvh_center[0] = bc[0]; v.bvh_center[1] = bc[1]; v.bvh_center[2] = bc[2];
-        v.bvh_r2 = br2; v.bvh_eps = beps; v.bvh_q = bq;
+        v.bvh_r2 = br2; v.bvh_eps = beps; v.bvh_q = bq; v.bvh_rmax = 1.0001f * brmax;
         for (int k = 0; k < 3; ++k) { v.bvh_qmin[k] = bin.qmin[k]; v.bvh_qstep[k] = qstep[k]; }
         c->stats.bvh_nodes = (uint32_t)(bin.count - 1);
         c->stats.accel_in_use = FORMA_RT_ACCEL_LBVH;

@@ -55,7 +55,8 @@ struct SceneView {
     float bvh_eps;             // absolute box pad: 2^-16 x scene scale
     float bvh_qmin[3];         // the tree's 16-bit grid: plane q on axis k lies at bvh_qmin[k] + q * bvh_qstep[k]
     float bvh_qstep[3];
-    float bvh_q;               // max 1/radius over the spheres of the tree (0 without spheres): scales the sphere pad
+    float bvh_q;               // max 1/|radius| over the spheres of the tree (0 without spheres): scales the sphere pad
+    float bvh_rmax;            // largest |radius| in the tree
     float cull_center[3];      // bounding sphere of every finite sphere and triangle (closest_hit's cull);
     float cull_r2;             // radius squared; +inf = never cull
     int n_segments;

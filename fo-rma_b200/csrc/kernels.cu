@@ -491,7 +491,7 @@ __global__ void __launch_bounds__(kBlock, FORMA_TREE_MIN_BLOCKS) render_tree_ker
             if (!scene_culled(S, o, d, a)) {
                 for (int i = 0; i < S.big_spheres; ++i) try_prim(S, sph, tri, i, o, d, a, closest, winner);
                 for (int i = 0; i < S.big_tris; ++i) try_prim(S, sph, tri, S.n_spheres + i, o, d, a, closest, winner);
-                park(ray_grid(S, o, d));
+                park(ray_grid(S, o, d, a, closest));
                 node = 0; sp = 0;
                 phase = kWalk;
             }

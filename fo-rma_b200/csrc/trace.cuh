@@ -330,24 +330,49 @@ __device__ __forceinline__ QNode load_node(const uint4* __restrict__ nodes, int 
 //     Blo_k = (qmin_k - pad - o_k) / d_k,  Bhi_k = (qmin_k + pad - o_k) / d_k
 // - one FFMA per plane straight from the 16-bit value.  Exactness: a child box is visited iff the ray's
 // interval through the PADDED box reaches [0, closest]; pad = coef(ray) * q_tree + eps with
-// coef = 2^-19 (|o - C|^2 + R^2), q_tree = max 1/r over the spheres of the tree: it exceeds the largest miss
-// distance at which the f32 test of sphere.rs:25-29 can still report disc > 0 (|disc error| <= 25 eps_f32 a L^2,
-// L <= |o - C| + R), and eps = 2^-16 x scene scale covers the triangle test's rounding and that of the two
+// coef = 2^-20 L^2, q_tree = max 1/|r| over the spheres of the tree, L = a bound on |o - c| for every sphere the
+// walk could still accept: the smallest of (i) |o - C| + R for the tree's bounding sphere (as 2 (|o - C|^2 + R^2)),
+// (ii) the distance to the farthest corner of the tree's box, (iii) |d| closest_so_far + r_max at the START of the
+// walk - a root <= closest_so_far puts the sphere's centre that close, and on scenes with a floor every downward
+// ray arrives with the floor's hit already found (the outsized primitives are scanned first).  It exceeds the largest miss
+// distance at which the f32 test of sphere.rs:25-29 can still report disc > 0: term by term (u = 2^-24; b = oc.d
+// +-3u |oc||d|, b b +-7u a L^2, c = oc.oc - r r +-5u L^2, a c +-9u a L^2, the final subtraction +-u a L^2) the
+// computed disc is within 17 u a L^2 of a (r^2 - rho^2), which is below -2 a r delta for a ray that misses by delta,
+// so delta > 8.5 u L^2 / r is safe and the pad is 1.9x that.  Round 1 used (i) alone; (ii) alone is no tighter
+// (33.5 against 33.2 visits per ray on config D); (iii) is what shrinks the pad (profiles/r06d_*, r06e_*).
+// eps = 2^-16 x scene scale covers the triangle test's rounding and that of the two
 // roundings in q * A + B (each <= 1 ulp of |o_k / d_k| in t, i.e. <= 2^-23 |o_k| in space).  The grid itself is
 // conservative by construction (lbvh.cu rounds lo down and hi up by a whole extra cell).  So no primitive the
 // scan would accept is culled, and the tie rule makes the visiting order irrelevant.
+#ifndef FORMA_PAD_NEAR
+#define FORMA_PAD_NEAR 1   // 0 = without the closest_so_far bound on |o - c| (A/B switch)
+#endif
 struct RayGrid {
     float ax, ay, az;        // A_k
     float blx, bly, blz;     // Blo_k
     float bhx, bhy, bhz;     // Bhi_k
 };
-__device__ __forceinline__ RayGrid ray_grid(const SceneView& S, float3 o, float3 d) {
+__device__ __forceinline__ RayGrid ray_grid(const SceneView& S, float3 o, float3 d, float a, float closest) {
     const float huge = 1e30f;
     const float ix = fabsf(d.x) < 1e-30f ? copysignf(huge, d.x) : 1.0f / d.x;
     const float iy = fabsf(d.y) < 1e-30f ? copysignf(huge, d.y) : 1.0f / d.y;
     const float iz = fabsf(d.z) < 1e-30f ? copysignf(huge, d.z) : 1.0f / d.z;
+    // |o - c|^2 of every sphere that can still be accepted is bounded three ways; the smallest wins
     const float3 oc = o - f3(S.bvh_center);
-    const float pad = __fmaf_rn(1.9073486e-6f * (dot(oc, oc) + S.bvh_r2), S.bvh_q, S.bvh_eps);  // 2^-19 (...) q + eps
+    float L2 = 2.0f * (dot(oc, oc) + S.bvh_r2);            // centre inside the tree's bounding sphere
+    {
+        const float lx = S.bvh_qmin[0] - o.x, hx = __fmaf_rn(65535.0f, S.bvh_qstep[0], S.bvh_qmin[0]) - o.x;
+        const float ly = S.bvh_qmin[1] - o.y, hy = __fmaf_rn(65535.0f, S.bvh_qstep[1], S.bvh_qmin[1]) - o.y;
+        const float lz = S.bvh_qmin[2] - o.z, hz = __fmaf_rn(65535.0f, S.bvh_qstep[2], S.bvh_qmin[2]) - o.z;
+        L2 = fminf(L2, fmaxf(lx * lx, hx * hx) + fmaxf(ly * ly, hy * hy) + fmaxf(lz * lz, hz * hz));  // farthest corner of its box
+    }
+#if FORMA_PAD_NEAR
+    {   // a root <= closest_so_far puts the centre within |d| closest + r_max of the origin (NaN / inf: fminf keeps L2)
+        const float ln = __fmaf_rn(sqrtf(a), closest, S.bvh_rmax);
+        L2 = fminf(L2, 1.0001f * (ln * ln));
+    }
+#endif
+    const float pad = __fmaf_rn(9.5367432e-7f * L2, S.bvh_q, S.bvh_eps);  // 2^-20 L^2 q + eps
     RayGrid g;
     g.ax = S.bvh_qstep[0] * ix; g.ay = S.bvh_qstep[1] * iy; g.az = S.bvh_qstep[2] * iz;
     g.blx = (S.bvh_qmin[0] - pad - o.x) * ix; g.bhx = (S.bvh_qmin[0] + pad - o.x) * ix;
@@ -413,7 +438,7 @@ __device__ __forceinline__ bool beam_culled(const forma_rt_camera& c, const Scen
 __device__ __forceinline__ void bvh_closest(const SceneView& S, const float4* __restrict__ sph,
                                             const float4* __restrict__ tri, float3 o, float3 d, float a,
                                             HitState& h, Winner& w) {
-    const RayGrid g = ray_grid(S, o, d);
+    const RayGrid g = ray_grid(S, o, d, a, h.closest);  // a = d.d; closest: what the scan has found before the tree
     int stack[64];
     int sp = 0;
     int node = 0;
